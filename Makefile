@@ -1,0 +1,59 @@
+# Build everything in-tree (the built .so/binaries travel to the GPU box with the gpurun snapshot).
+#   make            -> libgfd_b200.so, gpu-feature-discovery, fake NVML, oracle C helpers
+#   make asan       -> ASan/UBSan build of the host-only parts under build/asan (tests use it when present)
+NVCC      ?= /usr/local/cuda/bin/nvcc
+CXX       ?= g++
+CC        ?= gcc
+CUDA_INC  ?= /usr/local/cuda/include
+PKG       := gpu-feature-discovery_b200
+CSRC      := $(PKG)/csrc
+GENCODE   := -gencode arch=compute_100a,code=sm_100a
+NVCCFLAGS := $(GENCODE) -O3 -lineinfo -std=c++17 -Iinclude -I$(CSRC) --fmad=false \
+             -Xcompiler -fPIC,-fvisibility=hidden,-Wall,-Wextra,-ffp-contract=off -Xptxas -v
+CXXFLAGS  := -O2 -std=c++17 -Wall -Wextra -fPIC -Iinclude -ffp-contract=off
+
+LIB       := $(PKG)/libgfd_b200.so
+BIN       := $(PKG)/gpu-feature-discovery
+FAKE      := $(PKG)/fake_nvml/lib/libnvidia-ml.so.1
+FAKE_NOMIG:= $(PKG)/fake_nvml/lib_nomig/libnvidia-ml.so.1
+ORACLE_SO := oracle/libgfd_oracle_c.so
+REPLAY    := oracle/ref_replay
+
+LIB_SRCS  := $(CSRC)/gfd_nvml.cpp $(CSRC)/gfd_mig_profile.cpp $(CSRC)/gfd_cuda_mgr.cpp $(CSRC)/gfd_probe.cu
+LABELER_SRCS := $(wildcard $(PKG)/labeler/*.cpp)
+
+TARGETS := $(LIB) $(FAKE) $(FAKE_NOMIG) $(ORACLE_SO)
+ifneq ($(wildcard oracle/ref_replay.c),)
+TARGETS += $(REPLAY)
+endif
+ifneq ($(LABELER_SRCS),)
+TARGETS += $(BIN)
+endif
+
+all: $(TARGETS)
+
+$(LIB): $(LIB_SRCS) $(CSRC)/gfd_internal.h include/gfd_b200.h
+	$(NVCC) $(NVCCFLAGS) -shared -cudart static -x cu $(LIB_SRCS) -o $@ -ldl -lpthread 2> build/ptxas_$(notdir $@).log || (cat build/ptxas_$(notdir $@).log; false)
+	@grep -E "registers|spill" build/ptxas_$(notdir $@).log | sort | uniq -c | head -20
+
+$(FAKE): $(PKG)/fake_nvml/fake_nvml.c
+	@mkdir -p $(dir $@)
+	$(CC) -O2 -Wall -Wextra -fPIC -shared -fvisibility=hidden -Wl,-soname,libnvidia-ml.so.1 -I$(CUDA_INC) -o $@ $< -lpthread
+
+$(FAKE_NOMIG): $(PKG)/fake_nvml/fake_nvml.c
+	@mkdir -p $(dir $@)
+	$(CC) -O2 -Wall -Wextra -fPIC -shared -fvisibility=hidden -Wl,-soname,libnvidia-ml.so.1 -DFAKE_NO_MIG_SYMBOLS -I$(CUDA_INC) -o $@ $< -lpthread
+
+$(ORACLE_SO): oracle/checksum_oracle.c
+	$(CC) -O2 -Wall -Wextra -fPIC -shared -o $@ $<
+
+$(REPLAY): oracle/ref_replay.c
+	$(CC) -O2 -Wall -Wextra -I$(CUDA_INC) -o $@ $< -ldl -lm
+
+$(BIN): $(LABELER_SRCS) $(LIB) include/gfd_b200.h
+	$(CXX) $(CXXFLAGS) -fPIE $(LABELER_SRCS) -o $@ -L$(PKG) -lgfd_b200 -Wl,-rpath,'$$ORIGIN' -lpthread
+
+clean:
+	rm -f $(LIB) $(BIN) $(FAKE) $(FAKE_NOMIG) $(ORACLE_SO) $(REPLAY)
+
+.PHONY: all clean

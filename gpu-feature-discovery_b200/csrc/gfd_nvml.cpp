@@ -1,0 +1,636 @@
+// NVML-backed resource.Manager / resource.Device for libgfd_b200.so.
+//
+// Replaces, behind the C ABI of include/gfd_b200.h:
+//   internal/resource/nvml-lib.go:24-97, nvml-device.go:26-88, nvml-mig-device.go:27-134   (adapters)
+//   V/nvlib/nvlib/device/device.go:55-118,192-236,288-298,326-338, mig_device.go:40-148    (walks, profile)
+//   V/nvlib/nvml/*.go, V/go-nvml/nvml/{init.go:33-72,127-218, device.go, system.go}, dl/dl.go:51-82 (binding)
+//
+// Design (not a port): the reference re-walks all devices 4x per pass and opens/closes libnvidia-ml
+// once per IsMigCapable/IsMigEnabled call.  Here every distinct (NVML function, handle) pair the
+// reference would call is issued AT MOST ONCE per Init..Shutdown bracket and its status+value cached,
+// so (a) a pass needs ~1/3 of the calls and no dlopen cycles, (b) per-GPU prefetch can run on host
+// threads, and (c) the set of passes that fail is unchanged: an error is reported by the getter that
+// the reference's control flow would have reached, never earlier.
+#include <dlfcn.h>
+#include <sys/stat.h>
+
+#include <cstdio>
+#include <cstring>
+#include <thread>
+
+#include "gfd_internal.h"
+
+using namespace gfd;
+
+namespace {
+
+template <class F>
+void sym(void *lib, const char *name, F *out) {
+    *out = reinterpret_cast<F>(dlsym(lib, name));
+}
+template <class F>
+void sym2(void *lib, const char *preferred, const char *fallback, F *out) {
+    sym(lib, preferred, out);
+    if (!*out) sym(lib, fallback, out);
+}
+
+int load_nvml(NvmlApi *nv) {
+    // V/go-nvml/nvml/init.go:21-24,33-44: dlopen RTLD_LAZY|RTLD_GLOBAL; failure => ERROR_LIBRARY_NOT_FOUND
+    void *lib = dlopen("libnvidia-ml.so.1", RTLD_LAZY | RTLD_GLOBAL);
+    if (!lib) return NVML_ERROR_LIBRARY_NOT_FOUND;
+    *nv = NvmlApi();
+    nv->lib = lib;
+    sym(lib, "nvmlInit_v2", &nv->Init_v2);
+    sym(lib, "nvmlInit", &nv->Init_v1);
+    sym(lib, "nvmlShutdown", &nv->Shutdown);
+    sym(lib, "nvmlErrorString", &nv->ErrorString);
+    sym(lib, "nvmlSystemGetDriverVersion", &nv->SystemGetDriverVersion);
+    sym(lib, "nvmlSystemGetCudaDriverVersion", &nv->SystemGetCudaDriverVersion);
+    sym2(lib, "nvmlDeviceGetCount_v2", "nvmlDeviceGetCount", &nv->DeviceGetCount);
+    sym2(lib, "nvmlDeviceGetHandleByIndex_v2", "nvmlDeviceGetHandleByIndex", &nv->DeviceGetHandleByIndex);
+    sym(lib, "nvmlDeviceGetName", &nv->DeviceGetName);
+    sym(lib, "nvmlDeviceGetMemoryInfo", &nv->DeviceGetMemoryInfo);
+    sym(lib, "nvmlDeviceGetCudaComputeCapability", &nv->DeviceGetCudaComputeCapability);
+    sym(lib, "nvmlDeviceGetMigMode", &nv->DeviceGetMigMode);
+    sym(lib, "nvmlDeviceGetMaxMigDeviceCount", &nv->DeviceGetMaxMigDeviceCount);
+    sym(lib, "nvmlDeviceGetMigDeviceHandleByIndex", &nv->DeviceGetMigDeviceHandleByIndex);
+    sym(lib, "nvmlDeviceIsMigDeviceHandle", &nv->DeviceIsMigDeviceHandle);
+    sym(lib, "nvmlDeviceGetDeviceHandleFromMigDeviceHandle", &nv->DeviceGetDeviceHandleFromMigDeviceHandle);
+    sym2(lib, "nvmlDeviceGetAttributes_v2", "nvmlDeviceGetAttributes", &nv->DeviceGetAttributes);
+    sym(lib, "nvmlDeviceGetGpuInstanceId", &nv->DeviceGetGpuInstanceId);
+    sym(lib, "nvmlDeviceGetComputeInstanceId", &nv->DeviceGetComputeInstanceId);
+    sym(lib, "nvmlDeviceGetGpuInstanceById", &nv->DeviceGetGpuInstanceById);
+    sym(lib, "nvmlGpuInstanceGetInfo", &nv->GpuInstanceGetInfo);
+    sym(lib, "nvmlGpuInstanceGetComputeInstanceById", &nv->GpuInstanceGetComputeInstanceById);
+    sym2(lib, "nvmlComputeInstanceGetInfo_v2", "nvmlComputeInstanceGetInfo", &nv->ComputeInstanceGetInfo);
+    sym(lib, "nvmlDeviceGetGpuInstanceProfileInfo", &nv->DeviceGetGpuInstanceProfileInfo);
+    sym(lib, "nvmlGpuInstanceGetComputeInstanceProfileInfo", &nv->GpuInstanceGetComputeInstanceProfileInfo);
+    sym(lib, "nvmlDeviceGetUUID", &nv->DeviceGetUUID);
+    return 0;
+}
+
+// The manager whose NVML is currently initialised, for gfd_strerror (errorStringFunc swap, V/nvlib/nvml/nvml.go:44-49)
+std::atomic<gfd_mgr *> g_live_mgr{nullptr};
+
+#define NVCALL(m, fn, ...) ((m)->nvml_calls.fetch_add(1, std::memory_order_relaxed), \
+                            (m)->nv.fn ? (int)(m)->nv.fn(__VA_ARGS__) : (int)NVML_ERROR_FUNCTION_NOT_FOUND)
+
+size_t clen(const char *b, size_t n) {  // V/go-nvml/nvml/cgo_helpers: first NUL or the whole buffer
+    size_t i = 0;
+    while (i < n && b[i]) i++;
+    return i;
+}
+
+// ---- per-device cached getters ------------------------------------------------------------------
+int q_name_raw(gfd_dev *d) {  // nvmlDeviceGetName with the reference's 96-byte buffer (V/go-nvml/nvml/device.go:60-64)
+    if (!d->name.done) {
+        char buf[NVML_DEVICE_NAME_V2_BUFFER_SIZE];
+        memset(buf, 0, sizeof buf);
+        d->name.rc = NVCALL(d->mgr, DeviceGetName, d->h, buf, (unsigned)sizeof buf);
+        d->name.v.assign(buf, clen(buf, sizeof buf));
+        d->name.done = true;
+    }
+    return d->name.rc;
+}
+
+int q_mem(gfd_dev *d) {
+    if (!d->mem_total_bytes.done) {
+        nvmlMemory_t mem;
+        memset(&mem, 0, sizeof mem);
+        d->mem_total_bytes.rc = NVCALL(d->mgr, DeviceGetMemoryInfo, d->h, &mem);
+        d->mem_total_bytes.v = mem.total;
+        d->mem_total_bytes.done = true;
+    }
+    return d->mem_total_bytes.rc;
+}
+
+int q_cc(gfd_dev *d) {
+    if (!d->cc.done) {
+        int major = 0, minor = 0;
+        d->cc.rc = NVCALL(d->mgr, DeviceGetCudaComputeCapability, d->h, &major, &minor);
+        d->cc.v = {major, minor};
+        d->cc.done = true;
+    }
+    return d->cc.rc;
+}
+
+int q_mig_mode(gfd_dev *d) {
+    // device.go:55-88.  nvmlLookupSymbol's dlopen/dlsym/dlclose cycle (device.go:326-338) collapses to the
+    // dlsym done once at load; a missing symbol or NOT_SUPPORTED means "not capable", not an error.
+    if (!d->mig_mode.done) {
+        d->mig_mode.done = true;
+        d->mgr->dl_probes.fetch_add(1, std::memory_order_relaxed);
+        if (!d->mgr->nv.DeviceGetMigMode) {
+            d->mig_mode.rc = 0;
+            d->mig_mode.v.supported = false;
+            return 0;
+        }
+        unsigned cur = 0, pend = 0;
+        int rc = NVCALL(d->mgr, DeviceGetMigMode, d->h, &cur, &pend);
+        if (rc == NVML_ERROR_NOT_SUPPORTED) {
+            d->mig_mode.rc = 0;
+            d->mig_mode.v.supported = false;
+        } else {
+            d->mig_mode.rc = rc;
+            d->mig_mode.v.supported = (rc == 0);
+            d->mig_mode.v.current = cur;
+            d->mig_mode.v.pending = pend;
+        }
+    }
+    return d->mig_mode.rc;
+}
+
+int q_migs(gfd_dev *d) {
+    // device.go:91-118 (VisitMigDevices) + mig_device.go:40-49 (NewMigDevice)
+    if (!d->migs.done) {
+        d->migs.done = true;
+        unsigned count = 0;
+        int rc = NVCALL(d->mgr, DeviceGetMaxMigDeviceCount, d->h, &count);
+        if (rc) { d->migs.rc = rc; return rc; }
+        for (unsigned i = 0; i < count; i++) {
+            nvmlDevice_t mh = nullptr;
+            rc = NVCALL(d->mgr, DeviceGetMigDeviceHandleByIndex, d->h, i, &mh);
+            if (rc == NVML_ERROR_NOT_FOUND || rc == NVML_ERROR_INVALID_ARGUMENT) continue;
+            if (rc) { d->migs.rc = rc; d->migs.v.clear(); return rc; }
+            unsigned is_mig = 0;
+            rc = NVCALL(d->mgr, DeviceIsMigDeviceHandle, mh, &is_mig);
+            if (rc) { d->migs.rc = rc; d->migs.v.clear(); return rc; }
+            if (!is_mig) { d->migs.rc = GFD_ERR_NOT_A_MIG_HANDLE; d->migs.v.clear(); return d->migs.rc; }
+            std::unique_ptr<gfd_dev> m(new gfd_dev());
+            m->mgr = d->mgr;
+            m->is_mig = true;
+            m->h = mh;
+            m->parent = d;
+            d->migs.v.push_back(std::move(m));
+        }
+    }
+    return d->migs.rc;
+}
+
+int q_attrs(gfd_dev *m) {
+    if (!m->attrs.done) {
+        memset(&m->attrs.v, 0, sizeof m->attrs.v);
+        m->attrs.rc = NVCALL(m->mgr, DeviceGetAttributes, m->h, &m->attrs.v);
+        m->attrs.done = true;
+    }
+    return m->attrs.rc;
+}
+
+int q_parent_handle(gfd_dev *m) {
+    if (!m->parent_handle.done) {
+        m->parent_handle.v = nullptr;
+        m->parent_handle.rc = NVCALL(m->mgr, DeviceGetDeviceHandleFromMigDeviceHandle, m->h, &m->parent_handle.v);
+        m->parent_handle.done = true;
+    }
+    return m->parent_handle.rc;
+}
+
+// Parent device wrapper for property queries on the handle NVML returned.  On every real node that handle
+// is the one the MIG device was enumerated from, so the enumerating gfd_dev (and its cache) is reused.
+gfd_dev *parent_wrapper(gfd_dev *m) {
+    if (m->parent && m->parent->h == m->parent_handle.v) return m->parent;
+    if (!m->parent_dev.done) {
+        m->parent_dev.done = true;
+        m->parent_dev.v.reset(new gfd_dev());
+        m->parent_dev.v->mgr = m->mgr;
+        m->parent_dev.v->h = m->parent_handle.v;
+    }
+    return m->parent_dev.v.get();
+}
+
+// migdevice.GetProfile (mig_device.go:52-148) + nvmlMigDevice.GetName (nvml-mig-device.go:96-104)
+int q_mig_profile_name(gfd_dev *m) {
+    if (m->name.done) return m->name.rc;
+    m->name.done = true;
+    gfd_mgr *g = m->mgr;
+    int rc;
+    auto fail = [&](int code) { m->name.rc = code; return code; };
+
+    if ((rc = q_parent_handle(m))) return fail(rc);
+    gfd_dev *p = parent_wrapper(m);
+    if ((rc = q_mem(p))) return fail(rc);
+    if ((rc = q_attrs(m))) return fail(rc);
+    unsigned gi_id = 0, ci_id = 0;
+    if ((rc = NVCALL(g, DeviceGetGpuInstanceId, m->h, &gi_id))) return fail(rc);
+    if ((rc = NVCALL(g, DeviceGetComputeInstanceId, m->h, &ci_id))) return fail(rc);
+
+    GiEntry &gi = p->gis[gi_id];
+    if (!gi.handle.done) {
+        gi.handle.done = true;
+        gi.handle.v = nullptr;
+        gi.handle.rc = NVCALL(g, DeviceGetGpuInstanceById, p->h, gi_id, &gi.handle.v);
+    }
+    if (gi.handle.rc) return fail(gi.handle.rc);
+    nvmlComputeInstance_t ci = nullptr;
+    if ((rc = NVCALL(g, GpuInstanceGetComputeInstanceById, gi.handle.v, ci_id, &ci))) return fail(rc);
+    if (!gi.profile_id.done) {
+        gi.profile_id.done = true;
+        nvmlGpuInstanceInfo_t info;
+        memset(&info, 0, sizeof info);
+        gi.profile_id.rc = NVCALL(g, GpuInstanceGetInfo, gi.handle.v, &info);
+        gi.profile_id.v = info.profileId;
+    }
+    if (gi.profile_id.rc) return fail(gi.profile_id.rc);
+    nvmlComputeInstanceInfo_t ci_info;
+    memset(&ci_info, 0, sizeof ci_info);
+    if ((rc = NVCALL(g, ComputeInstanceGetInfo, ci, &ci_info))) return fail(rc);
+
+    // The reference's NVML 11.x header bounds: ids >= 8 (e.g. B200 1g.45gb = 9) are never probed, so such
+    // a device ends in "no matching profile IDs found" -- reproduced on purpose (SURVEY.md Fact 4).
+    const unsigned kGiProfileCount = 8, kCiProfileCount = 7;  // V/go-nvml/nvml/const.go:555,571
+    for (unsigned i = 0; i < kGiProfileCount; i++) {
+        Cached<unsigned> &gp = p->gi_profile_info_id[i];
+        if (!gp.done) {
+            gp.done = true;
+            nvmlGpuInstanceProfileInfo_t info;
+            memset(&info, 0, sizeof info);
+            gp.rc = NVCALL(g, DeviceGetGpuInstanceProfileInfo, p->h, i, &info);
+            gp.v = info.id;
+        }
+        if (gp.rc == NVML_ERROR_NOT_SUPPORTED || gp.rc == NVML_ERROR_INVALID_ARGUMENT) continue;
+        if (gp.rc) return fail(gp.rc);
+        if (gp.v != gi.profile_id.v) continue;
+        for (unsigned j = 0; j < kCiProfileCount; j++) {
+            Cached<unsigned> &cp = gi.ci_profile_info_id[j];
+            if (!cp.done) {
+                cp.done = true;
+                nvmlComputeInstanceProfileInfo_t info;
+                memset(&info, 0, sizeof info);
+                cp.rc = NVCALL(g, GpuInstanceGetComputeInstanceProfileInfo, gi.handle.v, j, 0u, &info);
+                cp.v = info.id;
+            }
+            if (cp.rc == NVML_ERROR_NOT_SUPPORTED || cp.rc == NVML_ERROR_INVALID_ARGUMENT) continue;
+            if (cp.rc) return fail(cp.rc);
+            if (cp.v != ci_info.profileId) continue;
+            std::string prof;
+            // NB the loop INDICES (i, j), not the ids, are what the reference feeds NewMigProfile (mig_device.go:136)
+            if ((rc = mig_profile_string((int)i, (int)j, m->attrs.v.memorySizeMB, p->mem_total_bytes.v, &prof))) return fail(rc);
+            for (char &c : prof)
+                if (c == '+') c = '.';  // strings.ReplaceAll(p.String(), "+", ".")
+            m->name.v = prof;
+            m->name.rc = 0;
+            return 0;
+        }
+    }
+    return fail(GFD_ERR_NO_MATCHING_PROFILE);
+}
+
+int enumerate(gfd_mgr *m) {
+    // devicelib.VisitDevices (device.go:206-236) incl. isSkipped (device.go:192-203)
+    if (m->devices.done) return m->devices.rc;
+    m->devices.done = true;
+    unsigned count = 0;
+    int rc = NVCALL(m, DeviceGetCount, &count);
+    if (rc) return m->devices.rc = rc;
+    for (unsigned i = 0; i < count; i++) {
+        nvmlDevice_t h = nullptr;
+        rc = NVCALL(m, DeviceGetHandleByIndex, i, &h);
+        if (rc) { m->devices.v.clear(); return m->devices.rc = rc; }
+        std::unique_ptr<gfd_dev> d(new gfd_dev());
+        d->mgr = m;
+        d->h = h;
+        rc = q_name_raw(d.get());
+        if (rc) { m->devices.v.clear(); return m->devices.rc = rc; }
+        if (d->name.v == "NVIDIA DGX Display") continue;  // api.go:53-55
+        m->devices.v.push_back(std::move(d));
+    }
+    return m->devices.rc = 0;
+}
+
+void prefetch_one(gfd_dev *d) {
+    q_mem(d);
+    q_cc(d);
+    if (q_mig_mode(d) == 0 && d->mig_mode.v.supported && d->mig_mode.v.current == NVML_DEVICE_MIG_ENABLE) {
+        if (q_migs(d) == 0)
+            for (auto &mig : d->migs.v) {
+                q_mig_profile_name(mig.get());
+                q_attrs(mig.get());
+            }
+    }
+}
+
+#define CHECK_MGR(m) do { if (!(m)) return GFD_ERR_BAD_ARGUMENT; if (!(m)->initialized) return GFD_ERR_NOT_INITIALIZED; } while (0)
+#define CHECK_DEV(d) do { if (!(d) || !(d)->mgr) return GFD_ERR_BAD_ARGUMENT; if (!(d)->mgr->initialized) return GFD_ERR_NOT_INITIALIZED; } while (0)
+
+}  // namespace
+
+namespace gfd {
+int copy_out(const std::string &s, char *buf, size_t len) {
+    if (!buf || len == 0) return GFD_ERR_BAD_ARGUMENT;
+    if (s.size() + 1 > len) {
+        memcpy(buf, s.data(), len - 1);
+        buf[len - 1] = 0;
+        return GFD_ERR_BUFFER_TOO_SMALL;
+    }
+    memcpy(buf, s.data(), s.size());
+    buf[s.size()] = 0;
+    return 0;
+}
+const char *nvml_error_string_if_loaded(int rc) {
+    gfd_mgr *m = g_live_mgr.load();
+    if (m && m->initialized && m->backend == GFD_BACKEND_NVML && m->nv.ErrorString) return m->nv.ErrorString((nvmlReturn_t)rc);
+    return nullptr;
+}
+}  // namespace gfd
+
+// ---- platform detection ---------------------------------------------------------------------------
+GFD_API int gfd_has_nvml(char *reason, size_t n) {
+    // info.HasNvml (V/nvlib/nvlib/info/info.go:41-53): dlopen RTLD_LAZY, close again
+    void *lib = dlopen("libnvidia-ml.so.1", RTLD_LAZY);
+    if (!lib) {
+        const char *e = dlerror();
+        if (reason && n) snprintf(reason, n, "could not load NVML: %s", e ? e : "unknown error");
+        return 0;
+    }
+    dlclose(lib);
+    if (reason && n) snprintf(reason, n, "found NVML library");
+    return 1;
+}
+
+GFD_API int gfd_is_tegra_system(const char *root, char *reason, size_t n) {
+    // info.IsTegraSystem (info.go:56-78)
+    std::string r = root ? root : "";
+    std::string release = r + "/etc/nv_tegra_release", family = r + "/sys/devices/soc0/family";
+    struct stat st;
+    auto say = [&](const std::string &s) { if (reason && n) snprintf(reason, n, "%s", s.c_str()); };
+    if (stat(release.c_str(), &st) == 0 && !S_ISDIR(st.st_mode)) { say(release + " found"); return 1; }
+    if (stat(family.c_str(), &st) != 0 || S_ISDIR(st.st_mode)) { say(family + " file not found"); return 0; }
+    FILE *f = fopen(family.c_str(), "rb");
+    if (!f) { say("could not read " + family); return 0; }
+    char buf[16] = {0};
+    size_t got = fread(buf, 1, 5, f);
+    fclose(f);
+    for (size_t i = 0; i < got; i++)
+        if (buf[i] >= 'A' && buf[i] <= 'Z') buf[i] = (char)(buf[i] - 'A' + 'a');
+    if (got == 5 && memcmp(buf, "tegra", 5) == 0) { say(family + " has 'tegra' prefix"); return 1; }
+    say(family + " has no 'tegra' prefix");
+    return 0;
+}
+
+// ---- manager ----------------------------------------------------------------------------------------
+GFD_API int gfd_mgr_new(int backend, unsigned flags, gfd_mgr **out) {
+    if (!out || backend < GFD_BACKEND_NVML || backend > GFD_BACKEND_NULL) return GFD_ERR_BAD_ARGUMENT;
+    gfd_mgr *m = new gfd_mgr();
+    m->backend = backend;
+    m->flags = flags;
+    *out = m;
+    return 0;
+}
+
+GFD_API void gfd_mgr_free(gfd_mgr *m) {
+    if (!m) return;
+    if (m->initialized) gfd_shutdown(m);
+    if (m->attached && m->nv.lib) {
+        if (m->nv.Shutdown) m->nv.Shutdown();
+        dlclose(m->nv.lib);
+        m->attached = false;
+    }
+    if (m->backend == GFD_BACKEND_CUDA) cuda_mgr_free(m);
+    gfd_mgr *self = m;
+    g_live_mgr.compare_exchange_strong(self, nullptr);
+    delete m;
+}
+
+GFD_API int gfd_init(gfd_mgr *m) {
+    if (!m) return GFD_ERR_BAD_ARGUMENT;
+    if (m->initialized) return 0;
+    m->nvml_calls = 0;
+    m->dl_probes = 0;
+    m->devices = {};
+    if (m->backend == GFD_BACKEND_NULL) { m->initialized = true; return 0; }  // null.go:35-37
+    if (m->backend == GFD_BACKEND_CUDA) {
+        int rc = cuda_mgr_init(m);
+        if (rc == 0) m->initialized = true;
+        return rc;
+    }
+    if (!m->attached) {
+        int rc = load_nvml(&m->nv);
+        if (rc) return rc;
+    }
+    m->nvml_calls++;
+    auto init = m->nv.Init_v2 ? m->nv.Init_v2 : m->nv.Init_v1;  // updateVersionedSymbols (init.go:127-131)
+    int rc = init ? (int)init() : (int)NVML_ERROR_FUNCTION_NOT_FOUND;
+    if (rc) {
+        // go-nvml leaves the library open on a failed nvmlInit (init.go:33-44); it leaks one handle per
+        // failed pass.  We close it: no observable difference, no leak.
+        if (!m->attached) { dlclose(m->nv.lib); m->nv = NvmlApi(); }
+        return rc;
+    }
+    if ((m->flags & GFD_MGR_KEEP_ATTACHED) && !m->attached) {
+        // one extra reference: NVML refcounts nvmlInit, so later brackets skip the driver attach
+        if (init() == NVML_SUCCESS) m->attached = true;
+    }
+    m->initialized = true;
+    g_live_mgr.store(m);
+    return 0;
+}
+
+GFD_API int gfd_shutdown(gfd_mgr *m) {
+    if (!m) return GFD_ERR_BAD_ARGUMENT;
+    if (!m->initialized) return (m->backend == GFD_BACKEND_NULL) ? 0 : GFD_ERR_NOT_INITIALIZED;
+    m->devices = {};  // handles die with the bracket
+    if (m->backend == GFD_BACKEND_NULL) { m->initialized = false; return 0; }
+    if (m->backend == GFD_BACKEND_CUDA) { m->initialized = false; return cuda_mgr_shutdown(m); }
+    int rc = NVCALL(m, Shutdown);
+    if (rc) return rc;  // init.go:61-64: library stays loaded, still "initialised"
+    m->initialized = false;
+    gfd_mgr *self = m;
+    g_live_mgr.compare_exchange_strong(self, nullptr);
+    if (!m->attached) {
+        dlclose(m->nv.lib);
+        m->nv = NvmlApi();
+    }
+    return 0;
+}
+
+GFD_API int gfd_driver_version(gfd_mgr *m, char *buf, size_t len) {
+    CHECK_MGR(m);
+    if (m->backend == GFD_BACKEND_NULL) return GFD_ERR_UNSUPPORTED_BACKEND;
+    if (m->backend == GFD_BACKEND_CUDA) return copy_out("unknown.unknown.unknown", buf, len);  // cuda-lib.go:66-68
+    char v[NVML_SYSTEM_DRIVER_VERSION_BUFFER_SIZE];
+    memset(v, 0, sizeof v);
+    int rc = NVCALL(m, SystemGetDriverVersion, v, (unsigned)sizeof v);
+    if (rc) return rc;
+    return copy_out(std::string(v, clen(v, sizeof v)), buf, len);
+}
+
+GFD_API int gfd_cuda_driver_version(gfd_mgr *m, unsigned *major, unsigned *minor) {
+    CHECK_MGR(m);
+    if (!major || !minor) return GFD_ERR_BAD_ARGUMENT;
+    if (m->backend == GFD_BACKEND_NULL) return GFD_ERR_UNSUPPORTED_BACKEND;
+    if (m->backend == GFD_BACKEND_CUDA) return cuda_mgr_driver_version(m, major, minor);
+    int v = 0;
+    int rc = NVCALL(m, SystemGetCudaDriverVersion, &v);
+    if (rc) return rc;
+    // nvml-lib.go:47-48 converts the Go int (64-bit) straight to uint
+    *major = (unsigned)(uint64_t)((int64_t)v / 1000);
+    *minor = (unsigned)(uint64_t)((int64_t)v % 1000 / 10);
+    return 0;
+}
+
+GFD_API int gfd_device_count(gfd_mgr *m, int *count) {
+    CHECK_MGR(m);
+    if (!count) return GFD_ERR_BAD_ARGUMENT;
+    if (m->backend == GFD_BACKEND_NULL) { *count = 0; return 0; }
+    int rc = (m->backend == GFD_BACKEND_CUDA) ? cuda_mgr_enumerate(m) : enumerate(m);
+    if (rc) return rc;
+    *count = (int)m->devices.v.size();
+    return 0;
+}
+
+GFD_API int gfd_device_get(gfd_mgr *m, int idx, gfd_dev **dev) {
+    int n = 0;
+    int rc = gfd_device_count(m, &n);
+    if (rc) return rc;
+    if (!dev || idx < 0 || idx >= n) return GFD_ERR_BAD_ARGUMENT;
+    *dev = m->devices.v[(size_t)idx].get();
+    return 0;
+}
+
+GFD_API int gfd_prefetch(gfd_mgr *m, int threads) {
+    CHECK_MGR(m);
+    if (m->backend != GFD_BACKEND_NVML || threads <= 1) return 0;
+    int rc = enumerate(m);
+    if (rc) return 0;  // reported by gfd_device_count, where the reference would see it
+    size_t n = m->devices.v.size();
+    if (n < 2) return 0;
+    std::atomic<size_t> next{0};
+    size_t nt = std::min(n, (size_t)threads);
+    std::vector<std::thread> pool;
+    for (size_t t = 0; t < nt; t++)
+        pool.emplace_back([&] {
+            for (size_t i = next.fetch_add(1); i < n; i = next.fetch_add(1)) prefetch_one(m->devices.v[i].get());
+        });
+    for (auto &t : pool) t.join();
+    return 0;
+}
+
+GFD_API int gfd_call_stats(gfd_mgr *m, uint64_t *nvml_calls, uint64_t *dl_probes) {
+    if (!m) return GFD_ERR_BAD_ARGUMENT;
+    if (nvml_calls) *nvml_calls = m->nvml_calls.load();
+    if (dl_probes) *dl_probes = m->dl_probes.load();
+    return 0;
+}
+
+// ---- devices ------------------------------------------------------------------------------------------
+GFD_API int gfd_dev_name(gfd_dev *d, char *buf, size_t len) {
+    CHECK_DEV(d);
+    int rc;
+    if (d->mgr->backend == GFD_BACKEND_CUDA) rc = cuda_dev_name(d);
+    else rc = d->is_mig ? q_mig_profile_name(d) : q_name_raw(d);
+    if (rc) return rc;
+    return copy_out(d->name.v, buf, len);
+}
+
+GFD_API int gfd_dev_total_memory_mb(gfd_dev *d, uint64_t *mb) {
+    CHECK_DEV(d);
+    if (!mb) return GFD_ERR_BAD_ARGUMENT;
+    if (d->is_mig) {  // nvml-mig-device.go:107-118
+        int rc = q_attrs(d);
+        if (rc) return rc;
+        *mb = d->attrs.v.memorySizeMB;
+        return 0;
+    }
+    int rc = (d->mgr->backend == GFD_BACKEND_CUDA) ? cuda_dev_mem(d) : q_mem(d);
+    if (rc) return rc;
+    *mb = d->mem_total_bytes.v / (1024ull * 1024ull);
+    return 0;
+}
+
+GFD_API int gfd_dev_cuda_compute_capability(gfd_dev *d, int *major, int *minor) {
+    CHECK_DEV(d);
+    if (!major || !minor) return GFD_ERR_BAD_ARGUMENT;
+    if (d->is_mig) return GFD_ERR_IS_MIG_DEVICE;
+    int rc = (d->mgr->backend == GFD_BACKEND_CUDA) ? cuda_dev_cc(d) : q_cc(d);
+    if (rc) return rc;
+    *major = d->cc.v.first;
+    *minor = d->cc.v.second;
+    return 0;
+}
+
+GFD_API int gfd_dev_is_mig_capable(gfd_dev *d, int *capable) {
+    CHECK_DEV(d);
+    if (!capable) return GFD_ERR_BAD_ARGUMENT;
+    if (d->is_mig) return GFD_ERR_IS_MIG_DEVICE;
+    if (d->mgr->backend == GFD_BACKEND_CUDA) { *capable = 0; return 0; }  // cuda-device.go:90-93
+    int rc = q_mig_mode(d);
+    if (rc) return rc;
+    *capable = d->mig_mode.v.supported ? 1 : 0;
+    return 0;
+}
+
+GFD_API int gfd_dev_is_mig_enabled(gfd_dev *d, int *enabled) {
+    CHECK_DEV(d);
+    if (!enabled) return GFD_ERR_BAD_ARGUMENT;
+    if (d->is_mig) return GFD_ERR_IS_MIG_DEVICE;
+    if (d->mgr->backend == GFD_BACKEND_CUDA) { *enabled = 0; return 0; }  // cuda-device.go:95-98
+    int rc = q_mig_mode(d);
+    if (rc) return rc;
+    *enabled = (d->mig_mode.v.supported && d->mig_mode.v.current == NVML_DEVICE_MIG_ENABLE) ? 1 : 0;
+    return 0;
+}
+
+GFD_API int gfd_dev_mig_count(gfd_dev *d, int *count) {
+    CHECK_DEV(d);
+    if (!count) return GFD_ERR_BAD_ARGUMENT;
+    if (d->is_mig) return GFD_ERR_IS_MIG_DEVICE;
+    if (d->mgr->backend == GFD_BACKEND_CUDA) return GFD_ERR_UNSUPPORTED_BACKEND;  // cuda-device.go:70-72
+    int rc = q_migs(d);
+    if (rc) return rc;
+    *count = (int)d->migs.v.size();
+    return 0;
+}
+
+GFD_API int gfd_dev_mig_get(gfd_dev *d, int idx, gfd_dev **mig) {
+    int n = 0;
+    int rc = gfd_dev_mig_count(d, &n);
+    if (rc) return rc;
+    if (!mig || idx < 0 || idx >= n) return GFD_ERR_BAD_ARGUMENT;
+    *mig = d->migs.v[(size_t)idx].get();
+    return 0;
+}
+
+GFD_API int gfd_dev_parent(gfd_dev *mig, gfd_dev **parent) {
+    CHECK_DEV(mig);
+    if (!parent) return GFD_ERR_BAD_ARGUMENT;
+    if (mig->mgr->backend == GFD_BACKEND_CUDA) return GFD_ERR_UNSUPPORTED_BACKEND;
+    if (!mig->is_mig) return GFD_ERR_NOT_MIG_DEVICE;
+    int rc = q_parent_handle(mig);
+    if (rc) return rc;
+    *parent = parent_wrapper(mig);
+    return 0;
+}
+
+GFD_API int gfd_dev_attributes(gfd_dev *mig, gfd_mig_attributes *out) {
+    CHECK_DEV(mig);
+    if (!out) return GFD_ERR_BAD_ARGUMENT;
+    if (mig->mgr->backend == GFD_BACKEND_CUDA) return GFD_ERR_UNSUPPORTED_BACKEND;
+    if (!mig->is_mig) return GFD_ERR_NOT_MIG_DEVICE;
+    int rc = q_attrs(mig);
+    if (rc) return rc;
+    const nvmlDeviceAttributes_t &a = mig->attrs.v;
+    out->memory_mb = a.memorySizeMB;
+    out->multiprocessors = a.multiprocessorCount;
+    out->slices_gi = a.gpuInstanceSliceCount;
+    out->slices_ci = a.computeInstanceSliceCount;
+    out->engines_copy = a.sharedCopyEngineCount;
+    out->engines_decoder = a.sharedDecoderCount;
+    out->engines_encoder = a.sharedEncoderCount;
+    out->engines_jpeg = a.sharedJpegCount;
+    out->engines_ofa = a.sharedOfaCount;
+    return 0;
+}
+
+GFD_API int gfd_dev_uuid(gfd_dev *d, char *buf, size_t len) {
+    CHECK_DEV(d);
+    if (d->mgr->backend != GFD_BACKEND_NVML) return GFD_ERR_UNSUPPORTED_BACKEND;
+    if (!d->uuid.done) {
+        d->uuid.done = true;
+        char u[NVML_DEVICE_UUID_V2_BUFFER_SIZE];
+        memset(u, 0, sizeof u);
+        d->uuid.rc = NVCALL(d->mgr, DeviceGetUUID, d->h, u, (unsigned)sizeof u);
+        d->uuid.v.assign(u, clen(u, sizeof u));
+    }
+    if (d->uuid.rc) return d->uuid.rc;
+    return copy_out(d->uuid.v, buf, len);
+}

@@ -1,0 +1,518 @@
+// Opt-in capability probes for libgfd_b200.so: hand-written sm_100a streaming kernels.
+//
+// NEW capability -- the reference (GFD v0.7.0) launches no GPU work; nothing here replaces reference code
+// and nothing here runs unless a probe flag / entry point asks for it (BASELINE.json north_star).
+//
+//   hbm_read_fold   stream N bytes from HBM with coalesced 128/256-bit loads, fold every 64-bit word into
+//                   (xor, sum) so the reads cannot be elided and the result is checkable against the CPU
+//                   oracle bit for bit.  Algorithmic traffic: N bytes read.       Roofline: HBM3e.
+//   hbm_copy        dst[i] = src[i] with the same access shape.  Traffic 2N.     Roofline: HBM3e (or
+//                   NVLink 5 when one side is a peer mapping -- that is the P2P probe's kernel).
+//   fill_pattern    word[i] = 0x9E3779B97F4A7C15 * (i + seed): deterministic, seedless probe input.
+//
+// Shape: persistent grid = SMs x kBlocksPerSM CTAs of kThreads threads; each CTA walks 64 KiB tiles
+// grid-stride; inside a tile every thread issues kUnroll independent 16-byte (or 8 x 32-byte) loads before
+// consuming any (>= 128 KiB in flight per SM, >> HBM latency x bandwidth / 148).  Loads bypass L1
+// (.nc.L1::no_allocate) and are marked evict-first in L2: each byte is touched once.
+#include <cuda_runtime.h>
+
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <mutex>
+
+#include "gfd_internal.h"
+
+namespace {
+
+constexpr int kThreads = 512;
+constexpr int kUnroll = 8;             // 16-byte loads in flight per thread
+constexpr int kBlocksPerSM = 2;
+constexpr int kMaxBlocks = 4096;       // scratch is sized for this many partials
+constexpr uint64_t kGolden = 0x9E3779B97F4A7C15ull;
+constexpr int kMaxDevices = 64;
+
+#define CUDA_TRY(expr) do { cudaError_t e__ = (expr); if (e__ != cudaSuccess) return GFD_ERR_CUDA + (int)e__; } while (0)
+
+struct U2 { uint64_t a, b; };
+
+// 128-bit streaming load: no L1 allocation, evict-first in L2 through a cache-policy operand (the bare
+// .L2::evict_first qualifier exists only on the 256-bit form below).
+__device__ __forceinline__ uint64_t evict_first_policy() {
+    uint64_t pol;
+    asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
+    return pol;
+}
+__device__ __forceinline__ U2 ld_stream16(const void *p, uint64_t pol) {
+    U2 r;
+    asm volatile("ld.global.nc.L1::no_allocate.L2::cache_hint.v2.u64 {%0,%1}, [%2], %3;"
+                 : "=l"(r.a), "=l"(r.b) : "l"(p), "l"(pol));
+    return r;
+}
+__device__ __forceinline__ void ld_stream32(const void *p, U2 &lo, U2 &hi) {
+    asm volatile("ld.global.nc.L1::no_allocate.L2::evict_first.v4.u64 {%0,%1,%2,%3}, [%4];"
+                 : "=l"(lo.a), "=l"(lo.b), "=l"(hi.a), "=l"(hi.b) : "l"(p));
+}
+__device__ __forceinline__ void st_stream16(void *p, U2 v) {
+    asm volatile("st.global.L1::no_allocate.v2.u64 [%0], {%1,%2};" ::"l"(p), "l"(v.a), "l"(v.b) : "memory");
+}
+
+struct Fold {
+    uint64_t x = 0, s = 0;
+    __device__ __forceinline__ void add(uint64_t w) { x ^= w; s += w; }
+    __device__ __forceinline__ void add(U2 v) { add(v.a); add(v.b); }
+};
+
+__device__ __forceinline__ void block_reduce_store(Fold f, ulonglong2 *partials) {
+    for (int o = 16; o > 0; o >>= 1) {
+        f.x ^= __shfl_xor_sync(0xffffffffu, f.x, o);
+        f.s += __shfl_xor_sync(0xffffffffu, f.s, o);
+    }
+    __shared__ uint64_t sx[kThreads / 32], ss[kThreads / 32];
+    int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (lane == 0) { sx[warp] = f.x; ss[warp] = f.s; }
+    __syncthreads();
+    if (warp == 0) {
+        uint64_t x = lane < kThreads / 32 ? sx[lane] : 0, s = lane < kThreads / 32 ? ss[lane] : 0;
+        for (int o = 16; o > 0; o >>= 1) {
+            x ^= __shfl_xor_sync(0xffffffffu, x, o);
+            s += __shfl_xor_sync(0xffffffffu, s, o);
+        }
+        if (lane == 0) partials[blockIdx.x] = make_ulonglong2(x, s);
+    }
+}
+
+// n16 = number of whole 16-byte vectors; the < 16 tail bytes are folded by the finishing kernel.
+template <bool kWide>
+__global__ void __launch_bounds__(kThreads, kBlocksPerSM)
+hbm_read_fold_kernel(const char *__restrict__ src, size_t n16, ulonglong2 *__restrict__ partials) {
+    constexpr size_t kTile = (size_t)kThreads * kUnroll;  // 16-byte vectors per tile (64 KiB)
+    const size_t full_tiles = n16 / kTile;
+    Fold f;
+    const uint64_t pol = evict_first_policy();
+    for (size_t t = blockIdx.x; t < full_tiles; t += gridDim.x) {
+        const char *base = src + t * kTile * 16;
+        U2 v[kUnroll];
+        if (kWide) {
+#pragma unroll
+            for (int j = 0; j < kUnroll / 2; j++)
+                ld_stream32(base + ((size_t)j * kThreads + threadIdx.x) * 32, v[2 * j], v[2 * j + 1]);
+        } else {
+#pragma unroll
+            for (int j = 0; j < kUnroll; j++) v[j] = ld_stream16(base + ((size_t)j * kThreads + threadIdx.x) * 16, pol);
+        }
+#pragma unroll
+        for (int j = 0; j < kUnroll; j++) f.add(v[j]);
+    }
+    // ragged remainder (< one tile), bounds-checked, spread over the whole grid
+    for (size_t i = full_tiles * kTile + (size_t)blockIdx.x * kThreads + threadIdx.x; i < n16;
+         i += (size_t)gridDim.x * kThreads)
+        f.add(ld_stream16(src + i * 16, pol));
+    block_reduce_store(f, partials);
+}
+
+// One CTA: fold the per-block partials and the < 16 tail bytes (zero-padded to 64-bit words) into *out.
+__global__ void __launch_bounds__(256) fold_finish_kernel(const ulonglong2 *__restrict__ partials, int n_partials,
+                                                          const unsigned char *__restrict__ tail, int tail_bytes,
+                                                          gfd_checksum *__restrict__ out) {
+    uint64_t x = 0, s = 0;
+    for (int i = threadIdx.x; i < n_partials; i += blockDim.x) {
+        ulonglong2 p = partials[i];
+        x ^= p.x;
+        s += p.y;
+    }
+    if (threadIdx.x == 0 && tail_bytes > 0) {
+        uint64_t w[2] = {0, 0};
+        for (int b = 0; b < tail_bytes; b++) w[b >> 3] |= (uint64_t)tail[b] << (8 * (b & 7));
+        x ^= w[0]; s += w[0];
+        if (tail_bytes > 8) { x ^= w[1]; s += w[1]; }
+    }
+    for (int o = 16; o > 0; o >>= 1) {
+        x ^= __shfl_xor_sync(0xffffffffu, x, o);
+        s += __shfl_xor_sync(0xffffffffu, s, o);
+    }
+    __shared__ uint64_t sx[8], ss[8];
+    int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (lane == 0) { sx[warp] = x; ss[warp] = s; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        uint64_t X = 0, S = 0;
+        for (int i = 0; i < 8; i++) { X ^= sx[i]; S += ss[i]; }
+        out->xor64 = X;
+        out->sum64 = S;
+    }
+}
+
+__global__ void __launch_bounds__(kThreads, kBlocksPerSM)
+hbm_copy_kernel(char *__restrict__ dst, const char *__restrict__ src, size_t n16, int tail_bytes) {
+    constexpr size_t kTile = (size_t)kThreads * kUnroll;
+    const size_t full_tiles = n16 / kTile;
+    const uint64_t pol = evict_first_policy();
+    for (size_t t = blockIdx.x; t < full_tiles; t += gridDim.x) {
+        const size_t off = t * kTile * 16;
+        U2 v[kUnroll];
+#pragma unroll
+        for (int j = 0; j < kUnroll; j++) v[j] = ld_stream16(src + off + ((size_t)j * kThreads + threadIdx.x) * 16, pol);
+#pragma unroll
+        for (int j = 0; j < kUnroll; j++) st_stream16(dst + off + ((size_t)j * kThreads + threadIdx.x) * 16, v[j]);
+    }
+    for (size_t i = full_tiles * kTile + (size_t)blockIdx.x * kThreads + threadIdx.x; i < n16;
+         i += (size_t)gridDim.x * kThreads)
+        st_stream16(dst + i * 16, ld_stream16(src + i * 16, pol));
+    if (blockIdx.x == 0 && threadIdx.x < tail_bytes) dst[n16 * 16 + threadIdx.x] = src[n16 * 16 + threadIdx.x];
+}
+
+__global__ void __launch_bounds__(kThreads, kBlocksPerSM)
+fill_pattern_kernel(char *__restrict__ dst, size_t n16, int tail_bytes, uint64_t seed) {
+    for (size_t i = (size_t)blockIdx.x * kThreads + threadIdx.x; i < n16; i += (size_t)gridDim.x * kThreads) {
+        U2 v;
+        v.a = kGolden * (2 * i + seed);
+        v.b = kGolden * (2 * i + 1 + seed);
+        st_stream16(dst + i * 16, v);
+    }
+    if (blockIdx.x == 0 && threadIdx.x < tail_bytes) {
+        uint64_t w = kGolden * (2 * n16 + (threadIdx.x >> 3) + seed);
+        dst[n16 * 16 + threadIdx.x] = (char)(w >> (8 * (threadIdx.x & 7)));
+    }
+}
+
+// ---- host side --------------------------------------------------------------------------------------
+struct DevInfo { int sms = 0; bool ok = false; };
+DevInfo g_dev[kMaxDevices];
+std::mutex g_mu;
+
+int device_info(int dev, DevInfo *out) {
+    if (dev < 0 || dev >= kMaxDevices) return GFD_ERR_BAD_ARGUMENT;
+    std::lock_guard<std::mutex> lk(g_mu);
+    if (!g_dev[dev].ok) {
+        int sms = 0;
+        CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+        g_dev[dev].sms = sms;
+        g_dev[dev].ok = true;
+    }
+    *out = g_dev[dev];
+    return 0;
+}
+
+int device_count_checked(int *n) {
+    int c = 0;
+    cudaError_t e = cudaGetDeviceCount(&c);
+    if (e != cudaSuccess || c <= 0) {
+        (void)cudaGetLastError();
+        return GFD_ERR_NO_GPU;  // no CPU fallback for GPU work
+    }
+    *n = c;
+    return 0;
+}
+
+int device_of_pointer(const void *p, int *dev) {
+    cudaPointerAttributes a;
+    cudaError_t e = cudaPointerGetAttributes(&a, p);
+    if (e != cudaSuccess) { (void)cudaGetLastError(); return GFD_ERR_CUDA + (int)e; }
+    if (a.type != cudaMemoryTypeDevice && a.type != cudaMemoryTypeManaged) return GFD_ERR_BAD_ARGUMENT;
+    *dev = a.device;
+    return 0;
+}
+
+struct DeviceScope {  // this library's static CUDA runtime keeps its own current device; set + restore it
+    int prev = -1;
+    int rc = 0;
+    explicit DeviceScope(int dev) {
+        cudaError_t e = cudaGetDevice(&prev);
+        if (e != cudaSuccess) { prev = -1; (void)cudaGetLastError(); }
+        e = cudaSetDevice(dev);
+        if (e != cudaSuccess) rc = GFD_ERR_CUDA + (int)e;
+    }
+    ~DeviceScope() { if (prev >= 0) cudaSetDevice(prev); }
+};
+
+int grid_for(int sms, size_t n16) {
+    constexpr size_t kTile = (size_t)kThreads * kUnroll;
+    size_t want = (n16 + kTile - 1) / kTile;
+    size_t cap = (size_t)sms * kBlocksPerSM;
+    if (cap > (size_t)kMaxBlocks) cap = kMaxBlocks;
+    if (want < 1) want = 1;
+    return (int)(want < cap ? want : cap);
+}
+
+bool wide_loads() {  // experiment knob; default chosen from profiles/ 
+    static int v = -1;
+    if (v < 0) { const char *e = getenv("GFD_B200_WIDE_LOADS"); v = e ? atoi(e) : 1; }
+    return v != 0;
+}
+
+int launch_read(int dev, const void *d_buf, size_t bytes, gfd_checksum *d_out, void *d_scratch, cudaStream_t st,
+                int *grid_out) {
+    DevInfo di;
+    int rc = device_info(dev, &di);
+    if (rc) return rc;
+    size_t n16 = bytes / 16;
+    int tail = (int)(bytes % 16);
+    int grid = grid_for(di.sms, n16);
+    auto *partials = static_cast<ulonglong2 *>(d_scratch);
+    bool wide = wide_loads() && ((uintptr_t)d_buf % 32 == 0);
+    if (wide)
+        hbm_read_fold_kernel<true><<<grid, kThreads, 0, st>>>(static_cast<const char *>(d_buf), n16, partials);
+    else
+        hbm_read_fold_kernel<false><<<grid, kThreads, 0, st>>>(static_cast<const char *>(d_buf), n16, partials);
+    CUDA_TRY(cudaGetLastError());
+    fold_finish_kernel<<<1, 256, 0, st>>>(partials, grid, static_cast<const unsigned char *>(d_buf) + n16 * 16, tail, d_out);
+    CUDA_TRY(cudaGetLastError());
+    if (grid_out) *grid_out = grid;
+    return 0;
+}
+
+int launch_copy(int dev, void *d_dst, const void *d_src, size_t bytes, cudaStream_t st, int *grid_out) {
+    DevInfo di;
+    int rc = device_info(dev, &di);
+    if (rc) return rc;
+    size_t n16 = bytes / 16;
+    int grid = grid_for(di.sms, n16);
+    hbm_copy_kernel<<<grid, kThreads, 0, st>>>(static_cast<char *>(d_dst), static_cast<const char *>(d_src), n16, (int)(bytes % 16));
+    CUDA_TRY(cudaGetLastError());
+    if (grid_out) *grid_out = grid;
+    return 0;
+}
+
+int launch_fill(int dev, void *d_buf, size_t bytes, uint64_t seed, cudaStream_t st) {
+    DevInfo di;
+    int rc = device_info(dev, &di);
+    if (rc) return rc;
+    size_t n16 = bytes / 16;
+    size_t want = (n16 + kThreads - 1) / kThreads;
+    size_t cap = (size_t)di.sms * kBlocksPerSM * 4;
+    int grid = (int)(want < 1 ? 1 : (want < cap ? want : cap));
+    fill_pattern_kernel<<<grid, kThreads, 0, st>>>(static_cast<char *>(d_buf), n16, (int)(bytes % 16), seed);
+    CUDA_TRY(cudaGetLastError());
+    return 0;
+}
+
+}  // namespace
+
+GFD_API size_t gfd_hbm_scratch_bytes(void) { return sizeof(ulonglong2) * (size_t)kMaxBlocks; }
+
+GFD_API int gfd_cuda_device_count(int *count) {
+    if (!count) return GFD_ERR_BAD_ARGUMENT;
+    return device_count_checked(count);
+}
+
+GFD_API int gfd_hbm_fill_pattern(void *d_buf, size_t bytes, uint64_t seed, void *stream) {
+    int n, dev;
+    int rc = device_count_checked(&n);
+    if (rc) return rc;
+    if (bytes == 0) return 0;
+    if (!d_buf) return GFD_ERR_BAD_ARGUMENT;
+    if ((uintptr_t)d_buf % 16) return GFD_ERR_ALIGNMENT;
+    if ((rc = device_of_pointer(d_buf, &dev))) return rc;
+    DeviceScope scope(dev);
+    if (scope.rc) return scope.rc;
+    return launch_fill(dev, d_buf, bytes, seed, static_cast<cudaStream_t>(stream));
+}
+
+GFD_API int gfd_hbm_read_checksum(const void *d_buf, size_t bytes, gfd_checksum *d_out, void *d_scratch,
+                                  size_t scratch_bytes, void *stream) {
+    int n, dev;
+    int rc = device_count_checked(&n);
+    if (rc) return rc;
+    if (!d_out || !d_scratch || (bytes && !d_buf)) return GFD_ERR_BAD_ARGUMENT;
+    if (scratch_bytes < gfd_hbm_scratch_bytes()) return GFD_ERR_BUFFER_TOO_SMALL;
+    if ((uintptr_t)d_buf % 16 || (uintptr_t)d_scratch % 16 || (uintptr_t)d_out % 8) return GFD_ERR_ALIGNMENT;
+    if ((rc = device_of_pointer(d_out, &dev))) return rc;
+    DeviceScope scope(dev);
+    if (scope.rc) return scope.rc;
+    return launch_read(dev, d_buf, bytes, d_out, d_scratch, static_cast<cudaStream_t>(stream), nullptr);
+}
+
+GFD_API int gfd_hbm_copy(void *d_dst, const void *d_src, size_t bytes, void *stream) {
+    int n, dev;
+    int rc = device_count_checked(&n);
+    if (rc) return rc;
+    if (bytes == 0) return 0;
+    if (!d_dst || !d_src) return GFD_ERR_BAD_ARGUMENT;
+    if ((uintptr_t)d_dst % 16 || (uintptr_t)d_src % 16) return GFD_ERR_ALIGNMENT;
+    if ((rc = device_of_pointer(d_dst, &dev))) return rc;
+    DeviceScope scope(dev);
+    if (scope.rc) return scope.rc;
+    return launch_copy(dev, d_dst, d_src, bytes, static_cast<cudaStream_t>(stream), nullptr);
+}
+
+// ---- host-buffer form ---------------------------------------------------------------------------------
+namespace {
+struct Staging {
+    void *d_buf = nullptr;
+    size_t cap = 0;
+    void *d_scratch = nullptr;
+    gfd_checksum *d_out = nullptr;
+    cudaStream_t st = nullptr;
+};
+Staging g_staging[kMaxDevices];
+std::mutex g_staging_mu;
+constexpr size_t kHostPathMax = 16ull << 30;  // 16 GiB per call
+}  // namespace
+
+GFD_API int gfd_checksum_host(int cuda_device, const void *host_buf, size_t bytes, gfd_checksum *out) {
+    int n;
+    int rc = device_count_checked(&n);
+    if (rc) return rc;
+    if (!out || (bytes && !host_buf) || cuda_device < 0 || cuda_device >= n || cuda_device >= kMaxDevices) return GFD_ERR_BAD_ARGUMENT;
+    if (bytes > kHostPathMax) return GFD_ERR_SIZE_LIMIT;
+    DeviceScope scope(cuda_device);
+    if (scope.rc) return scope.rc;
+    std::lock_guard<std::mutex> lk(g_staging_mu);  // staging is shared per device: one host-path call at a time
+    Staging &s = g_staging[cuda_device];
+    if (!s.st) {
+        CUDA_TRY(cudaStreamCreateWithFlags(&s.st, cudaStreamNonBlocking));
+        CUDA_TRY(cudaMalloc(&s.d_scratch, gfd_hbm_scratch_bytes()));
+        CUDA_TRY(cudaMalloc((void **)&s.d_out, sizeof(gfd_checksum)));
+    }
+    size_t need = (bytes + 255) / 256 * 256;
+    if (need > s.cap) {
+        if (s.d_buf) CUDA_TRY(cudaFree(s.d_buf));
+        s.d_buf = nullptr;
+        s.cap = 0;
+        CUDA_TRY(cudaMalloc(&s.d_buf, need));
+        s.cap = need;
+    }
+    if (bytes) CUDA_TRY(cudaMemcpyAsync(s.d_buf, host_buf, bytes, cudaMemcpyHostToDevice, s.st));
+    rc = launch_read(cuda_device, s.d_buf, bytes, s.d_out, s.d_scratch, s.st, nullptr);
+    if (rc) return rc;
+    CUDA_TRY(cudaMemcpyAsync(out, s.d_out, sizeof(gfd_checksum), cudaMemcpyDeviceToHost, s.st));
+    CUDA_TRY(cudaStreamSynchronize(s.st));
+    return 0;
+}
+
+// ---- self-contained probes ----------------------------------------------------------------------------
+namespace {
+struct Buf {
+    void *p = nullptr;
+    ~Buf() { if (p) cudaFree(p); }
+};
+struct Ev {
+    cudaEvent_t e = nullptr;
+    ~Ev() { if (e) cudaEventDestroy(e); }
+};
+struct Stream {
+    cudaStream_t s = nullptr;
+    ~Stream() { if (s) cudaStreamDestroy(s); }
+};
+
+// Time `iters` launches of the read/copy kernel running on `run_dev`; src may live on another device.
+int time_kernel(int run_dev, void *dst, const void *src, size_t bytes, int warmup, int iters, int mode,
+                gfd_probe_result *out) {
+    DeviceScope scope(run_dev);
+    if (scope.rc) return scope.rc;
+    DevInfo di;
+    int rc = device_info(run_dev, &di);
+    if (rc) return rc;
+    Stream st;
+    CUDA_TRY(cudaStreamCreateWithFlags(&st.s, cudaStreamNonBlocking));
+    Buf scratch, d_out;
+    CUDA_TRY(cudaMalloc(&scratch.p, gfd_hbm_scratch_bytes()));
+    CUDA_TRY(cudaMalloc(&d_out.p, sizeof(gfd_checksum)));
+    Ev e0, e1;
+    CUDA_TRY(cudaEventCreate(&e0.e));
+    CUDA_TRY(cudaEventCreate(&e1.e));
+    int grid = 0;
+    auto once = [&]() -> int {
+        if (mode == GFD_PROBE_COPY) return launch_copy(run_dev, dst, src, bytes, st.s, &grid);
+        return launch_read(run_dev, src, bytes, static_cast<gfd_checksum *>(d_out.p), scratch.p, st.s, &grid);
+    };
+    for (int i = 0; i < warmup; i++)
+        if ((rc = once())) return rc;
+    CUDA_TRY(cudaStreamSynchronize(st.s));
+    CUDA_TRY(cudaEventRecord(e0.e, st.s));
+    for (int i = 0; i < iters; i++)
+        if ((rc = once())) return rc;
+    CUDA_TRY(cudaEventRecord(e1.e, st.s));
+    CUDA_TRY(cudaEventSynchronize(e1.e));
+    float ms = 0;
+    CUDA_TRY(cudaEventElapsedTime(&ms, e0.e, e1.e));
+    memset(out, 0, sizeof *out);
+    out->bytes = bytes;
+    out->iters = iters;
+    out->mode = mode;
+    out->sm_count = di.sms;
+    out->grid = grid;
+    out->block = kThreads;
+    out->ms_per_launch = (double)ms / iters;
+    out->gbps = (double)bytes * iters / ((double)ms * 1e-3) / 1e9;
+    if (mode == GFD_PROBE_READ) CUDA_TRY(cudaMemcpy(&out->checksum, d_out.p, sizeof(gfd_checksum), cudaMemcpyDeviceToHost));
+    return 0;
+}
+}  // namespace
+
+GFD_API int gfd_probe_hbm(int cuda_device, size_t bytes, int warmup, int iters, int mode, gfd_probe_result *out) {
+    int n;
+    int rc = device_count_checked(&n);
+    if (rc) return rc;
+    if (!out || cuda_device < 0 || cuda_device >= n || bytes == 0 || iters <= 0 || warmup < 0 ||
+        (mode != GFD_PROBE_READ && mode != GFD_PROBE_COPY))
+        return GFD_ERR_BAD_ARGUMENT;
+    DeviceScope scope(cuda_device);
+    if (scope.rc) return scope.rc;
+    Buf src, dst;
+    CUDA_TRY(cudaMalloc(&src.p, bytes));
+    if (mode == GFD_PROBE_COPY) CUDA_TRY(cudaMalloc(&dst.p, bytes));
+    if ((rc = launch_fill(cuda_device, src.p, bytes, 0, nullptr))) return rc;
+    CUDA_TRY(cudaDeviceSynchronize());
+    rc = time_kernel(cuda_device, dst.p, src.p, bytes, warmup, iters, mode, out);
+    if (rc) return rc;
+    if (mode == GFD_PROBE_COPY) out->gbps *= 2.0;  // read + write both cross HBM
+    return 0;
+}
+
+GFD_API int gfd_probe_p2p(int src_device, int dst_device, size_t bytes, int warmup, int iters, int mode,
+                          gfd_probe_result *out) {
+    int n;
+    int rc = device_count_checked(&n);
+    if (rc) return rc;
+    if (!out || src_device < 0 || dst_device < 0 || src_device >= n || dst_device >= n || src_device == dst_device ||
+        bytes == 0 || iters <= 0 || warmup < 0 || (mode != GFD_PROBE_READ && mode != GFD_PROBE_COPY))
+        return GFD_ERR_BAD_ARGUMENT;
+    int can = 0;
+    CUDA_TRY(cudaDeviceCanAccessPeer(&can, dst_device, src_device));
+    if (!can) return GFD_ERR_PEER_ACCESS;
+    Buf src, dst;
+    {
+        DeviceScope s(src_device);
+        if (s.rc) return s.rc;
+        CUDA_TRY(cudaMalloc(&src.p, bytes));
+        if ((rc = launch_fill(src_device, src.p, bytes, 0, nullptr))) return rc;
+        CUDA_TRY(cudaDeviceSynchronize());
+    }
+    {
+        DeviceScope s(dst_device);
+        if (s.rc) return s.rc;
+        cudaError_t e = cudaDeviceEnablePeerAccess(src_device, 0);
+        if (e == cudaErrorPeerAccessAlreadyEnabled) (void)cudaGetLastError();
+        else if (e != cudaSuccess) return GFD_ERR_CUDA + (int)e;
+        if (mode == GFD_PROBE_COPY) CUDA_TRY(cudaMalloc(&dst.p, bytes));
+    }
+    rc = time_kernel(dst_device, dst.p, src.p, bytes, warmup, iters, mode, out);
+    {
+        DeviceScope s(src_device);  // free on the owning device
+        if (src.p) { cudaFree(src.p); src.p = nullptr; }
+    }
+    {
+        DeviceScope s(dst_device);
+        if (dst.p) { cudaFree(dst.p); dst.p = nullptr; }
+    }
+    return rc;
+}
+
+GFD_API int gfd_cuda_device_by_uuid(const char *uuid, int *ordinal) {
+    int n;
+    int rc = device_count_checked(&n);
+    if (rc) return rc;
+    if (!uuid || !ordinal) return GFD_ERR_BAD_ARGUMENT;
+    for (int d = 0; d < n; d++) {
+        cudaDeviceProp prop;
+        CUDA_TRY(cudaGetDeviceProperties(&prop, d));
+        const unsigned char *b = reinterpret_cast<const unsigned char *>(prop.uuid.bytes);
+        char s[64];
+        snprintf(s, sizeof s, "GPU-%02x%02x%02x%02x-%02x%02x-%02x%02x-%02x%02x-%02x%02x%02x%02x%02x%02x", b[0], b[1], b[2],
+                 b[3], b[4], b[5], b[6], b[7], b[8], b[9], b[10], b[11], b[12], b[13], b[14], b[15]);
+        if (strcmp(s, uuid) == 0) { *ordinal = d; return 0; }
+    }
+    return GFD_ERR_BAD_ARGUMENT;
+}

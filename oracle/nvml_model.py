@@ -192,8 +192,8 @@ class RawNvml:
 
     def shutdown(self):
         rc = self._rc("nvmlShutdown")
-        if rc == NVML_SUCCESS:
-            self.initialized -= 1
+        if rc != NVML_ERROR_UNINITIALIZED and self.initialized > 0:
+            self.initialized -= 1  # an injected error still tears down (same rule as fake_nvml.c)
         return rc, None
 
     def system_get_driver_version(self):

@@ -1,0 +1,199 @@
+"""-m gpu parity tests for the probe kernels: every call goes through the C ABI of libgfd_b200.so; the
+checker is the plain-C oracle (oracle/checksum_oracle.c) on the same bytes.  Bar: bit-exact (integer work).
+
+torch is used only as plumbing: device buffers, streams, host<->device copies."""
+import ctypes
+import importlib
+import os
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+@pytest.fixture(scope="module")
+def env():
+    import torch
+    assert torch.cuda.is_available(), "these tests need a B200"
+    B = importlib.import_module("gpu-feature-discovery_b200.binding")
+    so = os.path.join(ROOT, "oracle", "libgfd_oracle_c.so")
+    assert os.path.exists(so), "oracle/libgfd_oracle_c.so not built (make / __graft_entry__.build())"
+    orc = ctypes.CDLL(so)
+    orc.oracle_checksum.argtypes = [ctypes.c_void_p, ctypes.c_size_t, ctypes.POINTER(ctypes.c_uint64)]
+    orc.oracle_fill_pattern.argtypes = [ctypes.c_void_p, ctypes.c_size_t, ctypes.c_uint64]
+    orc.oracle_pattern_checksum.argtypes = [ctypes.c_size_t, ctypes.c_uint64, ctypes.POINTER(ctypes.c_uint64)]
+    dev = torch.device("cuda:0")
+    scratch = torch.empty(B.hbm_scratch_bytes(), dtype=torch.uint8, device=dev)
+    out = torch.zeros(2, dtype=torch.int64, device=dev)
+
+    class Env:
+        pass
+    e = Env()
+    e.torch, e.B, e.orc, e.dev, e.scratch, e.out = torch, B, orc, dev, scratch, out
+    return e
+
+
+def oracle_checksum(env, arr):
+    arr = np.ascontiguousarray(arr, dtype=np.uint8)
+    o = (ctypes.c_uint64 * 2)()
+    env.orc.oracle_checksum(arr.ctypes.data, arr.size, o)
+    return int(o[0]), int(o[1])
+
+
+def gpu_checksum(env, t, nbytes=None, stream=None):
+    torch = env.torch
+    nbytes = t.numel() * t.element_size() if nbytes is None else nbytes
+    st = torch.cuda.current_stream() if stream is None else stream
+    env.out.fill_(-1)
+    env.B.hbm_read_checksum(t.data_ptr(), nbytes, env.out.data_ptr(), env.scratch.data_ptr(), env.scratch.numel(), st.cuda_stream)
+    st.synchronize()
+    x, s = env.out.cpu().numpy().view(np.uint64)
+    return int(x), int(s)
+
+
+# sizes: empty, sub-word, sub-vector, ragged everywhere, exactly one 64 KiB tile, tile+-1, many tiles + tail
+SIZES = [0, 1, 7, 8, 15, 16, 17, 31, 32, 33, 4095, 4096, 65535, 65536, 65537, 65536 * 3 + 5, (1 << 20) + 13,
+         296 * 65536, 296 * 65536 + 65536 - 16, (64 << 20) + 9]
+
+
+@pytest.mark.parametrize("n", SIZES)
+def test_read_checksum_matches_oracle_random_bytes(env, n):
+    rng = np.random.default_rng(1234 + n)
+    host = rng.integers(0, 256, size=n, dtype=np.uint8)
+    t = env.torch.from_numpy(host).to(env.dev) if n else env.torch.empty(0, dtype=env.torch.uint8, device=env.dev)
+    assert gpu_checksum(env, t, n) == oracle_checksum(env, host)
+
+
+def test_read_checksum_unaligned_to_32_bytes(env):
+    """a 16-byte aligned (not 32-byte aligned) base must take the 128-bit path and still be exact"""
+    rng = np.random.default_rng(7)
+    n = (3 << 20) + 48
+    host = rng.integers(0, 256, size=n + 16, dtype=np.uint8)
+    t = env.torch.from_numpy(host).to(env.dev)
+    view = t[16:]
+    assert view.data_ptr() % 32 == 16
+    assert gpu_checksum(env, view, n) == oracle_checksum(env, host[16:])
+
+
+def test_misaligned_pointer_is_rejected(env):
+    t = env.torch.zeros(1024, dtype=env.torch.uint8, device=env.dev)
+    with pytest.raises(env.B.GfdError) as ei:
+        env.B.hbm_read_checksum(t.data_ptr() + 4, 512, env.out.data_ptr(), env.scratch.data_ptr(), env.scratch.numel(), 0)
+    assert ei.value.status == env.B.GFD_ERR_ALIGNMENT
+    with pytest.raises(env.B.GfdError) as ei:
+        env.B.hbm_read_checksum(t.data_ptr(), 512, env.out.data_ptr(), env.scratch.data_ptr(), 16, 0)
+    assert ei.value.status == env.B.GFD_ERR_BUFFER_TOO_SMALL
+
+
+@pytest.mark.parametrize("n", [0, 5, 16, 1000, 65536, 65536 * 5 + 7, (8 << 20) + 3])
+@pytest.mark.parametrize("seed", [0, 12345])
+def test_fill_pattern_matches_oracle(env, n, seed):
+    t = env.torch.zeros(max(n, 1) + 64, dtype=env.torch.uint8, device=env.dev)
+    env.B.hbm_fill_pattern(t.data_ptr(), n, seed, env.torch.cuda.current_stream().cuda_stream)
+    env.torch.cuda.synchronize()
+    got = t.cpu().numpy()
+    want = np.zeros(n, dtype=np.uint8)
+    env.orc.oracle_fill_pattern(want.ctypes.data, n, seed)
+    assert np.array_equal(got[:n], want)
+    assert not got[n:].any(), "fill wrote past the end"
+
+
+@pytest.mark.parametrize("n", [0, 1, 15, 16, 4097, 65536, 65536 * 7 + 9, (32 << 20) + 1])
+def test_copy_is_bit_exact(env, n):
+    rng = np.random.default_rng(99 + n)
+    host = rng.integers(0, 256, size=n, dtype=np.uint8)
+    src = env.torch.from_numpy(host).to(env.dev) if n else env.torch.empty(0, dtype=env.torch.uint8, device=env.dev)
+    dst = env.torch.full((n + 32,), 0xAB, dtype=env.torch.uint8, device=env.dev)
+    env.B.hbm_copy(dst.data_ptr(), src.data_ptr(), n, env.torch.cuda.current_stream().cuda_stream)
+    env.torch.cuda.synchronize()
+    got = dst.cpu().numpy()
+    assert np.array_equal(got[:n], host)
+    assert (got[n:] == 0xAB).all(), "copy wrote past the end"
+
+
+def test_full_size_properties_4gib(env):
+    """BASELINE probe size (4 GiB) through size-independent properties:
+    fill -> checksum equals the closed-form pattern checksum; copy -> same checksum; checksum of two halves
+    combines (xor / +) to the checksum of the whole; idempotent on repeat."""
+    torch, B = env.torch, env.B
+    n = 1 << 32
+    st = torch.cuda.current_stream().cuda_stream
+    buf = torch.empty(n, dtype=torch.uint8, device=env.dev)
+    B.hbm_fill_pattern(buf.data_ptr(), n, 0, st)
+    whole = gpu_checksum(env, buf)
+    o = (ctypes.c_uint64 * 2)()
+    env.orc.oracle_pattern_checksum(n // 8, 0, o)
+    assert whole == (int(o[0]), int(o[1]))
+    assert gpu_checksum(env, buf) == whole
+    half = n // 2
+    a = gpu_checksum(env, buf[:half], half)
+    b = gpu_checksum(env, buf[half:], half)
+    assert (a[0] ^ b[0], (a[1] + b[1]) % (1 << 64)) == whole
+    dst = torch.empty(n, dtype=torch.uint8, device=env.dev)
+    B.hbm_copy(dst.data_ptr(), buf.data_ptr(), n, st)
+    assert gpu_checksum(env, dst) == whole
+    # a single flipped byte anywhere must change the result
+    dst[n - 3] ^= 0x40
+    assert gpu_checksum(env, dst) != whole
+
+
+def test_checksum_on_side_stream(env):
+    torch = env.torch
+    rng = np.random.default_rng(5)
+    host = rng.integers(0, 256, size=(4 << 20) + 3, dtype=np.uint8)
+    t = torch.from_numpy(host).to(env.dev)
+    torch.cuda.synchronize()
+    s = torch.cuda.Stream()
+    assert gpu_checksum(env, t, host.size, stream=s) == oracle_checksum(env, host)
+
+
+def test_checksum_host_end_to_end(env):
+    """gfd_checksum_host: host buffer in, 16 bytes out; pinned and pageable sources."""
+    torch, B = env.torch, env.B
+    rng = np.random.default_rng(11)
+    for n in (0, 3, 1 << 20, (16 << 20) + 11):
+        host = rng.integers(0, 256, size=n, dtype=np.uint8)
+        want = oracle_checksum(env, host)
+        assert B.checksum_host(0, host.ctypes.data if n else 0, n) == want
+        if n:
+            pinned = torch.from_numpy(host).pin_memory()
+            assert B.checksum_host(0, pinned.data_ptr(), n) == want
+
+
+def test_probe_hbm_self_contained(env):
+    B = env.B
+    n = 1 << 30
+    r = B.probe_hbm(0, n, warmup=2, iters=5, mode=B.PROBE_READ)
+    o = (ctypes.c_uint64 * 2)()
+    env.orc.oracle_pattern_checksum(n // 8, 0, o)
+    assert r.checksum.tuple() == (int(o[0]), int(o[1]))
+    assert r.bytes == n and r.iters == 5 and r.sm_count >= 100 and r.grid == r.sm_count * 2
+    assert 500 < r.gbps < 20000, r.gbps
+    c = B.probe_hbm(0, n, warmup=2, iters=5, mode=B.PROBE_COPY)
+    assert 500 < c.gbps < 20000, c.gbps
+
+
+def test_probe_rejects_bad_arguments(env):
+    B = env.B
+    for args in ((99, 1 << 20, 1, 1, 0), (0, 0, 1, 1, 0), (0, 1 << 20, 1, 0, 0), (0, 1 << 20, 1, 1, 7)):
+        with pytest.raises(B.GfdError):
+            B.probe_hbm(*args[:2], warmup=args[2], iters=args[3], mode=args[4])
+
+
+def test_p2p_probe(env):
+    """NVLink peer probe: needs >= 2 GPUs (run with gpurun --gpus 2); the pulled bytes' checksum must equal
+    the pattern's closed form, i.e. every byte crossed the link intact."""
+    B = env.B
+    if env.torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    n = 1 << 28
+    r = B.probe_p2p(0, 1, n, warmup=2, iters=5, mode=B.PROBE_READ)
+    o = (ctypes.c_uint64 * 2)()
+    env.orc.oracle_pattern_checksum(n // 8, 0, o)
+    assert r.checksum.tuple() == (int(o[0]), int(o[1]))
+    assert 50 < r.gbps < 2000, r.gbps
+    c = B.probe_p2p(1, 0, n, warmup=2, iters=5, mode=B.PROBE_COPY)
+    assert 50 < c.gbps < 2000, c.gbps
