@@ -1,0 +1,246 @@
+"""The gpu-feature-discovery binary vs the oracle: label FILE parity on simulated nodes (CPU only).
+
+For every named node (tests/nodes.py) x MIG strategy the binary runs --oneshot against the fake
+libnvidia-ml.so.1 and its output file must equal the oracle's rendering byte for byte (the binary writes keys
+sorted; the oracle renders sorted -- SURVEY.md Fact 3).  Where the oracle says the reference fails, the binary
+must exit 1 and write nothing."""
+import json
+import os
+import stat
+
+import pytest
+
+import nodes as N
+from oracle import gfd_oracle as O, nvml_model as M
+from shimutil import B, run_cli, use_node
+
+NODES = N.nodes()
+CASES = [(n, s) for n in sorted(NODES) for s in N.STRATEGIES]
+GOLDEN = os.path.join(os.path.dirname(__file__), "golden")
+
+
+def cli_pass(tmp_path, node, strategy, extra_args=(), extra_env=None, machine=b"DGX B200\n", pci_root=None, nomig=False):
+    fix = use_node(node, tmp_path)
+    out = os.path.join(str(tmp_path), "features.d", "gfd")
+    os.makedirs(os.path.dirname(out), exist_ok=True)
+    mt = os.path.join(str(tmp_path), "product_name")
+    if machine is not None:
+        with open(mt, "wb") as f:
+            f.write(machine)
+    if pci_root is None:
+        pci_root = os.path.join(str(tmp_path), "pci-empty")
+        os.makedirs(pci_root, exist_ok=True)
+    env = {"GFD_FAKE_NVML": fix, "GFD_B200_PCI_DEVICES_ROOT": pci_root}
+    env.update(extra_env or {})
+    args = ["--oneshot", "--no-timestamp", "--mig-strategy=" + strategy, "--machine-type-file", mt, "-o", out] + list(extra_args)
+    rc, so, se = run_cli(args, env=env, nomig=nomig)
+    text = open(out).read() if os.path.exists(out) else None
+    return rc, text, se, out
+
+
+def oracle_pass(node, strategy, machine=b"DGX B200\n", time_slicing=(), pci=()):
+    cfg = O.Config(mig_strategy=strategy, no_timestamp=True, machine_type_file="/x", time_slicing=time_slicing)
+
+    def rf(_):
+        if machine is None:
+            raise OSError("no such file")
+        return machine
+    try:
+        labels, warnings = O.run_pass(O.NvmlManager(M.RawNvml(node)), list(pci), cfg, read_file=rf)
+        return O.render(labels), warnings
+    except O.GfdError:
+        return None, []
+
+
+@pytest.mark.parametrize("name,strategy", CASES, ids=["%s-%s" % c for c in CASES])
+def test_label_file_matches_oracle(name, strategy, tmp_path):
+    node = NODES[name]
+    want, _ = oracle_pass(node, strategy)
+    rc, got, stderr, out = cli_pass(tmp_path, node, strategy, nomig=bool(node.hidden))
+    if want is None:
+        assert rc == 1 and got is None, stderr
+        assert "Error: " in stderr
+    else:
+        assert rc == 0, stderr
+        assert got == want
+        assert stat.S_IMODE(os.stat(out).st_mode) == 0o644
+        assert os.path.isdir(os.path.join(os.path.dirname(out), "gfd-tmp"))        # oneshot leaves it behind
+        assert os.listdir(os.path.join(os.path.dirname(out), "gfd-tmp")) == []
+
+
+@pytest.mark.parametrize("name", ["c3_8xB200", "c4_single_8x7x1g23", "c5_mixed_hetero", "err_memory_on_non_representative_gpu", "gi_id9_but_other_gpu_empty"])
+@pytest.mark.parametrize("strategy", ["none", "single", "mixed"])
+def test_prefetch_threads_flag_same_output(name, strategy, tmp_path):
+    want, _ = oracle_pass(NODES[name], strategy)
+    rc, got, stderr, _ = cli_pass(tmp_path, NODES[name], strategy, extra_args=["--prefetch-threads=8"])
+    assert (got == want) and (rc == (1 if want is None else 0)), stderr
+
+
+def test_heterogeneous_node_output_is_one_the_reference_could_emit(tmp_path):
+    """Go map order makes the reference's output random on mixed-model nodes; ours must be one of its possibilities."""
+    for name in ("hetero_models", "hetero_mig_and_full"):
+        node = NODES[name]
+        cfg = O.Config(mig_strategy="mixed", no_timestamp=True, machine_type_file="/x")
+        possible = O.possible_label_sets(lambda: O.NvmlManager(M.RawNvml(node)), [], cfg, read_file=lambda p: b"DGX B200\n")
+        rc, got, stderr, _ = cli_pass(tmp_path, node, "mixed")
+        assert rc == 0 and got in possible, (stderr, len(possible))
+        assert len(possible) >= 2 or name != "hetero_models"
+
+
+@pytest.mark.parametrize("machine,want", [(b"NVIDIA DGX B200\n", "NVIDIA-DGX-B200"), (b"  PowerEdge XE9680 \r\n", "PowerEdge-XE9680"),
+                                          (b"", ""), (b"\xc2\xa0Odd\xe2\x80\x83Box\xc2\x85", "Odd Box"), (None, "unknown")])
+def test_machine_type(machine, want, tmp_path):
+    rc, got, stderr, _ = cli_pass(tmp_path, NODES["c2_1xB200"], "none", machine=machine)
+    assert rc == 0, stderr
+    oracle_text, _ = oracle_pass(NODES["c2_1xB200"], "none", machine=machine)
+    assert got == oracle_text
+    assert "nvidia.com/gpu.machine=%s\n" % want in got
+
+
+def test_machine_type_empty_path(tmp_path):
+    fix = use_node(NODES["c2_1xB200"], tmp_path)
+    out = os.path.join(str(tmp_path), "o")
+    empty = os.path.join(str(tmp_path), "pci-empty")
+    os.makedirs(empty)
+    rc, _, se = run_cli(["--oneshot", "--no-timestamp", "--machine-type-file=", "-o", out],
+                        env={"GFD_FAKE_NVML": fix, "GFD_B200_PCI_DEVICES_ROOT": empty})
+    assert rc == 0, se
+    assert "nvidia.com/gpu.machine=unknown\n" in open(out).read()
+
+
+# ---- time slicing through the config file -----------------------------------------------------------------
+def write_config(tmp_path, doc, name="config.yaml"):
+    p = os.path.join(str(tmp_path), name)
+    with open(p, "w") as f:
+        f.write(doc)
+    return p
+
+
+TS_CASES = [
+    ("gpu x2", "sharing:\n  timeSlicing:\n    resources:\n    - name: nvidia.com/gpu\n      replicas: 2\n",
+     [("nvidia.com/gpu", 2, "")]),
+    ("not matching", "sharing:\n  timeSlicing:\n    resources:\n    - name: nvidia.com/not-gpu\n      replicas: 2\n",
+     [("nvidia.com/not-gpu", 2, "")]),
+    ("rename is neutralised", "sharing:\n  timeSlicing:\n    resources:\n    - name: gpu\n      rename: gpu-shared\n      replicas: 4\n",
+     [("nvidia.com/gpu", 4, "")]),
+    ("renameByDefault keeps .shared", "sharing:\n  timeSlicing:\n    renameByDefault: true\n    resources:\n    - name: nvidia.com/gpu\n      replicas: 3\n",
+     [("nvidia.com/gpu", 3, "nvidia.com/gpu.shared")]),
+    ("mig resource", "version: v1\nsharing:\n  timeSlicing:\n    resources:\n    - name: nvidia.com/mig-1g.23gb\n      devices: [0, 1]\n      replicas: 5\n",
+     [("nvidia.com/mig-1g.23gb", 5, "")]),
+    ("json form", json.dumps({"version": "v1", "sharing": {"timeSlicing": {"resources": [{"name": "nvidia.com/gpu", "devices": "all", "replicas": 2}]}}}),
+     [("nvidia.com/gpu", 2, "")]),
+]
+
+
+@pytest.mark.parametrize("label,doc,ts", TS_CASES, ids=[c[0] for c in TS_CASES])
+@pytest.mark.parametrize("node,strategy", [("c2_1xB200", "none"), ("c4_single_8x7x1g23", "single"), ("c5_mixed_hetero", "mixed"),
+                                           ("c4_invalid_one_empty", "single")])
+def test_time_slicing(label, doc, ts, node, strategy, tmp_path):
+    cfg = write_config(tmp_path, doc)
+    want, _ = oracle_pass(NODES[node], strategy, time_slicing=[O.ReplicatedResource(n, r, rn) for n, r, rn in ts])
+    rc, got, stderr, _ = cli_pass(tmp_path, NODES[node], strategy, extra_args=["--config-file", cfg])
+    assert rc == 0, stderr
+    assert got == want
+
+
+# ---- vGPU through a sysfs tree -----------------------------------------------------------------------------
+VG = json.load(open(os.path.join(GOLDEN, "vgpu_blobs.json")))
+
+
+def make_pci_tree(tmp_path, devices):
+    root = os.path.join(str(tmp_path), "pci")
+    for addr, (vendor, klass, config) in devices.items():
+        d = os.path.join(root, addr)
+        os.makedirs(d)
+        open(os.path.join(d, "vendor"), "w").write(vendor + "\n")
+        if klass is not None:
+            open(os.path.join(d, "class"), "w").write(klass + "\n")
+        if config is not None:
+            open(os.path.join(d, "config"), "wb").write(config)
+    os.makedirs(root, exist_ok=True)
+    return root
+
+
+def oracle_pci(root):
+    return lambda: O.nvidia_pci_devices(root)
+
+
+def vgpu_case(tmp_path, devices, node="c2_1xB200"):
+    root = make_pci_tree(tmp_path, devices)
+    cfg = O.Config(no_timestamp=True, machine_type_file="/x")
+    try:
+        labels, _ = O.run_pass(O.NvmlManager(M.RawNvml(NODES[node])), oracle_pci(root), cfg, read_file=lambda p: b"DGX B200\n")
+        want = O.render(labels)
+    except O.GfdError as e:
+        want = None
+    rc, got, stderr, _ = cli_pass(tmp_path, NODES[node], "none", pci_root=root)
+    return want, rc, got, stderr
+
+
+def test_vgpu_reference_blobs_in_sysfs(tmp_path):
+    blobs = VG["blobs"]
+    want, rc, got, stderr = vgpu_case(tmp_path, {
+        "0000:00:01.0": ("0x8086", "0x060000", b"\x86\x80" + bytes(62)),                      # not NVIDIA: never read further
+        "0000:3b:00.0": ("0x10de", "0x030200", bytes.fromhex(blobs["gpuPassThroughConfig"])),
+        "0000:5e:00.0": ("0x10de", "0x030200", bytes.fromhex(blobs["vgpuConfig"])),
+    })
+    assert rc == 0 and got == want, stderr
+    assert "nvidia.com/vgpu.present=true\n" in got
+    assert "nvidia.com/vgpu.host-driver-version=%s\n" % VG["expect"]["host_driver_version"] in got
+    assert "nvidia.com/vgpu.host-driver-branch=%s\n" % VG["expect"]["host_driver_branch"] in got
+
+
+def test_vgpu_unprivileged_short_config_fails_the_pass(tmp_path):
+    """pciutil.go:116-118: < 256 bytes of config space (unprivileged container) is an error for ANY 0x10de function."""
+    want, rc, got, stderr = vgpu_case(tmp_path, {"0000:c0:00.0": ("0x10de", "0x030200", bytes.fromhex(VG["blobs"]["vgpuConfig"])[:64])})
+    assert want is None and rc == 1 and got is None
+    assert "privileged" in stderr
+
+
+def test_vgpu_with_no_nvml_devices_still_labels(tmp_path):
+    want, rc, got, stderr = vgpu_case(tmp_path, {"0000:5e:00.0": ("0x10de", "0x030200", bytes.fromhex(VG["blobs"]["vgpuConfig"]))}, node="zero_gpus")
+    assert rc == 0 and got == want and got.count("\n") == 3, stderr
+
+
+def _cfg_with_cap(cap_bytes, cap_pos=0xC8):
+    cfg = bytearray(256)
+    cfg[0:2] = b"\xde\x10"
+    cfg[0x06] = 0x10
+    cfg[0x34] = cap_pos
+    cfg[cap_pos:cap_pos + len(cap_bytes)] = cap_bytes
+    return bytes(cfg[:256]) if cap_pos + len(cap_bytes) <= 256 else bytes(cfg)
+
+
+VGPU_EDGE = {
+    "no capability list bit": bytes(6) + b"\x00" + bytes(249),
+    "chain loops": (lambda c: bytes(c))(bytearray(_cfg_with_cap(bytes([0x01, 0xC8, 0x08])))),
+    "chain broken 0xff": _cfg_with_cap(bytes([0xFF, 0x00, 0x08])),
+    "vendor cap, not VF": _cfg_with_cap(bytes([0x09, 0x00, 0x14, 0x01]) + bytes(16)),
+    "VF, high bytes in version": _cfg_with_cap(bytes([0x09, 0x00, 0x1B, 0x56, 0x46, 0x00, 0x16]) + b"5\xe9\xff.1\x80\x00\x00\x00\x00" + b"r\xc3\xa9_00\x00\x00\x00\x00"),
+    "VF, two records before version": _cfg_with_cap(bytes([0x09, 0x00, 0x23, 0x56, 0x46, 0x01, 0x04, 0xAA, 0xBB, 0x02, 0x04, 0xCC, 0xDD, 0x00, 0x16]) + b"535.54.03\x00" + b"r535_00\x00\x00\x00"),
+    "VF, version record truncated": _cfg_with_cap(bytes([0x09, 0x00, 0x10, 0x56, 0x46, 0x00, 0x16]) + b"535.54.03"),
+    "VF, zero-length record (reference would spin)": _cfg_with_cap(bytes([0x09, 0x00, 0x1B, 0x56, 0x46, 0x05, 0x00]) + bytes(20)),
+    "VF, record chain runs off the end": _cfg_with_cap(bytes([0x09, 0x00, 0x08, 0x56, 0x46, 0x05, 0x40, 0x00])),
+    "VF, capability exactly 5 bytes": _cfg_with_cap(bytes([0x09, 0x00, 0x05, 0x56, 0x46])),
+    "cap pointer at 0xFE": (lambda c: bytes(c))(bytearray(_cfg_with_cap(b"", 0xFE))),
+    "cap slice past len but within ReadFile cap": _cfg_with_cap(bytes([0x09, 0x00, 0x40, 0x56, 0x46, 0x00, 0x16]) + b"470.82.01\x00" + b"r470_00\x00\x00\x00", 0xE0),
+}
+
+
+@pytest.mark.parametrize("label", sorted(VGPU_EDGE), ids=sorted(VGPU_EDGE))
+def test_vgpu_edge_cases(label, tmp_path):
+    want, rc, got, stderr = vgpu_case(tmp_path, {"0000:5e:00.0": ("0x10de", "0x030200", VGPU_EDGE[label])})
+    if want is None:
+        assert rc == 1 and got is None, stderr
+    else:
+        assert rc == 0 and got == want, stderr
+
+
+def test_missing_pci_root_fails(tmp_path):
+    rc, got, stderr, _ = cli_pass(tmp_path, NODES["c2_1xB200"], "none", pci_root=os.path.join(str(tmp_path), "nope"))
+    assert rc == 1 and got is None and "unable to read PCI bus devices" in stderr
+
+
+def test_nvidia_function_without_class_file_fails(tmp_path):
+    want, rc, got, stderr = vgpu_case(tmp_path, {"0000:5e:00.0": ("0x10de", None, bytes(256))})
+    assert want is None and rc == 1
