@@ -59,6 +59,8 @@ static const std::vector<FlagDef> &flag_defs() {
         {"keep-nvml-attached", {}, Kind::Bool, "false", {"GFD_KEEP_NVML_ATTACHED"},
          "[b200, opt-in] keep NVML initialised between labeling passes instead of re-attaching every pass", true},
         {"timing", {}, Kind::Bool, "false", {"GFD_TIMING"}, "[b200, opt-in] log the wall-clock time of every labeling pass", true},
+        {"passes", {}, Kind::Int, "0", {"GFD_PASSES"},
+         "[b200, opt-in] label this many times (sleeping --sleep-interval in between), keep the file and exit; 0 = run until signalled", true},
         {"help", {"h"}, Kind::Bool, "false", {}, "show help", false},
         {"version", {"v"}, Kind::Bool, "false", {}, "print the version", false},
     };
@@ -583,6 +585,7 @@ Config load_config(const ParsedFlags &f) {
     c.prefetch_threads = (int)strtoll(f.str("prefetch-threads").c_str(), nullptr, 0);
     c.keep_nvml_attached = f.boolean("keep-nvml-attached");
     c.timing = f.boolean("timing");
+    c.passes = (int)strtoll(f.str("passes").c_str(), nullptr, 0);
     if (const char *root = getenv("GFD_B200_PCI_DEVICES_ROOT")) c.pci_devices_root = root;
     return c;
 }

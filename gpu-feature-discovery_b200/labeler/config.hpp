@@ -62,6 +62,7 @@ struct Config {  // V/spec/config.go:33-38, flags.go:43-72
     int prefetch_threads = 0;        // --prefetch-threads: per-GPU enumeration threads (0 = serial)
     bool keep_nvml_attached = false; // --keep-nvml-attached
     bool timing = false;             // --timing: log per-phase wall-clock of every pass
+    int passes = 0;                  // --passes N: exit (keeping the file) after N passes; 0 = daemon
     std::string pci_devices_root = "/sys/bus/pci/devices";  // GFD_B200_PCI_DEVICES_ROOT (test hook)
 
     std::string to_json() const;  // json.MarshalIndent(config, "", "  ") as main.go:127 prints it

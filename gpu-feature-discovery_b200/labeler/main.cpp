@@ -39,7 +39,7 @@ bool run(gfdlm::Manager &mgr, const gfdcfg::Config &config, const sigset_t &sigs
     struct Cleanup {  // the deferred removeOutputFile (main.go:149-156)
         const gfdcfg::Config &c;
         ~Cleanup() {
-            if (!*c.oneshot && !c.output_file->empty()) {
+            if (!*c.oneshot && c.passes <= 0 && !c.output_file->empty()) {
                 try {
                     gfdlm::remove_output_file(*c.output_file);
                 } catch (const gfdlm::PassError &e) {
@@ -55,6 +55,7 @@ bool run(gfdlm::Manager &mgr, const gfdcfg::Config &config, const sigset_t &sigs
     // NEW opt-in probes: also once per run(); they allocate GPU memory and take tens of ms per GPU
     gfdlm::Labels probes = gfdlm::probe_labels(config);
 
+    int passes_done = 0;
     while (true) {
         double t0 = now_ms();
         gfdlm::Labels nvml = gfdlm::nvml_labels(mgr, config);  // lm.NewLabelers: the eager NVML part
@@ -82,6 +83,7 @@ bool run(gfdlm::Manager &mgr, const gfdcfg::Config &config, const sigset_t &sigs
         if (config.timing) logf("timing: pass %.3f ms (nvml %.3f, vgpu %.3f, write %.3f)", t3 - t0, t1 - t0, t2 - t1, t3 - t2);
 
         if (*config.oneshot) return false;
+        if (config.passes > 0 && ++passes_done >= config.passes) return false;
 
         logf("Sleeping for %s", gocompat::duration_string(*config.sleep_interval_ns).c_str());
         const int64_t ns = *config.sleep_interval_ns < 0 ? 0 : *config.sleep_interval_ns;
