@@ -1,0 +1,292 @@
+// Experiment harness (not product, not a bench): sweep launch shapes / load paths for the HBM read and copy
+// probes on one B200 and print GB/s per variant, so the product kernel's constants come from measurement.
+//   nvcc -gencode arch=compute_100a,code=sm_100a -O3 -std=c++17 -o tools/hbm_sweep tools/hbm_sweep.cu
+#include <cuda_runtime.h>
+
+#include <cstdint>
+#include <cstdio>
+#include <cstdlib>
+
+#define CK(x) do { cudaError_t e = (x); if (e != cudaSuccess) { printf("CUDA error %s at %s:%d\n", cudaGetErrorString(e), __FILE__, __LINE__); exit(1); } } while (0)
+
+struct U2 { uint64_t a, b; };
+
+__device__ __forceinline__ uint64_t policy_evict_first() {
+    uint64_t p;
+    asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(p));
+    return p;
+}
+template <int HINT>  // 0 plain nc, 1 nc + L1::no_allocate, 2 + L2 evict_first policy
+__device__ __forceinline__ U2 ld16(const void *p, uint64_t pol) {
+    U2 r;
+    if (HINT == 0) asm volatile("ld.global.nc.v2.u64 {%0,%1}, [%2];" : "=l"(r.a), "=l"(r.b) : "l"(p));
+    else if (HINT == 1) asm volatile("ld.global.nc.L1::no_allocate.v2.u64 {%0,%1}, [%2];" : "=l"(r.a), "=l"(r.b) : "l"(p));
+    else asm volatile("ld.global.nc.L1::no_allocate.L2::cache_hint.v2.u64 {%0,%1}, [%2], %3;" : "=l"(r.a), "=l"(r.b) : "l"(p), "l"(pol));
+    return r;
+}
+template <int HINT>
+__device__ __forceinline__ void st16(void *p, U2 v, uint64_t pol) {
+    if (HINT == 0) asm volatile("st.global.v2.u64 [%0], {%1,%2};" ::"l"(p), "l"(v.a), "l"(v.b) : "memory");
+    else if (HINT == 1) asm volatile("st.global.L1::no_allocate.v2.u64 [%0], {%1,%2};" ::"l"(p), "l"(v.a), "l"(v.b) : "memory");
+    else asm volatile("st.global.L1::no_allocate.L2::cache_hint.v2.u64 [%0], {%1,%2}, %3;" ::"l"(p), "l"(v.a), "l"(v.b), "l"(pol) : "memory");
+}
+
+template <int T, int U, int BPS, int HINT>
+__global__ void __launch_bounds__(T, BPS) read_ldg(const char *__restrict__ src, size_t n16, ulonglong2 *out) {
+    constexpr size_t kTile = (size_t)T * U;
+    const size_t tiles = n16 / kTile;
+    uint64_t x = 0, s = 0;
+    const uint64_t pol = policy_evict_first();
+    for (size_t t = blockIdx.x; t < tiles; t += gridDim.x) {
+        const char *base = src + t * kTile * 16;
+        U2 v[U];
+#pragma unroll
+        for (int j = 0; j < U; j++) v[j] = ld16<HINT>(base + ((size_t)j * T + threadIdx.x) * 16, pol);
+#pragma unroll
+        for (int j = 0; j < U; j++) { x ^= v[j].a ^ v[j].b; s += v[j].a + v[j].b; }
+    }
+    if (x == 0x1234567 && s == 0x7654321) out[blockIdx.x * T + threadIdx.x] = make_ulonglong2(x, s);  // never true for the pattern
+    if (threadIdx.x == 0 && blockIdx.x == 0) out[0] = make_ulonglong2(x, s);
+}
+
+template <int T, int U, int BPS, int LH, int SH>
+__global__ void __launch_bounds__(T, BPS) copy_ldg(char *__restrict__ dst, const char *__restrict__ src, size_t n16) {
+    constexpr size_t kTile = (size_t)T * U;
+    const size_t tiles = n16 / kTile;
+    const uint64_t pol = policy_evict_first();
+    for (size_t t = blockIdx.x; t < tiles; t += gridDim.x) {
+        const size_t off = t * kTile * 16;
+        U2 v[U];
+#pragma unroll
+        for (int j = 0; j < U; j++) v[j] = ld16<LH>(src + off + ((size_t)j * T + threadIdx.x) * 16, pol);
+#pragma unroll
+        for (int j = 0; j < U; j++) st16<SH>(dst + off + ((size_t)j * T + threadIdx.x) * 16, v[j], pol);
+    }
+}
+
+// ---- TMA bulk (cp.async.bulk, UBLKCP) ring: 1 producer warp + CW consumer warps ------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t *b, int count) { asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(b)), "r"(count)); }
+__device__ __forceinline__ void mbar_expect_tx(uint64_t *b, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(b)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t *b) { asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(b)) : "memory"); }
+__device__ __forceinline__ void mbar_wait(uint64_t *b, uint32_t parity) {
+    asm volatile(
+        "{\n.reg .pred p;\nWAIT_LOOP:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra DONE;\nbra WAIT_LOOP;\nDONE:\n}\n" ::"r"(smem_u32(b)), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(void *smem_dst, const void *gsrc, uint32_t bytes, uint64_t *bar, uint64_t pol) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;" ::"r"(smem_u32(smem_dst)),
+                 "l"(gsrc), "r"(bytes), "r"(smem_u32(bar)), "l"(pol) : "memory");
+}
+__device__ __forceinline__ void bulk_s2g(void *gdst, const void *smem_src, uint32_t bytes) {
+    asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(gdst), "r"(smem_u32(smem_src)), "r"(bytes) : "memory");
+}
+
+template <int STAGES, int CHUNK, int CW>
+__global__ void __launch_bounds__((CW + 1) * 32, 1) read_tma(const char *__restrict__ src, size_t n_chunks, ulonglong2 *out) {
+    extern __shared__ __align__(128) unsigned char smem[];
+    __shared__ uint64_t full[STAGES], empty[STAGES];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < STAGES; s++) { mbar_init(&full[s], 1); mbar_init(&empty[s], CW); }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+    const size_t mine = n_chunks > blockIdx.x ? (n_chunks - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
+    uint64_t x = 0, s64 = 0;
+    if (warp == CW) {
+        if (lane == 0) {
+            const uint64_t pol = policy_evict_first();
+            for (size_t k = 0; k < mine; k++) {
+                int st = (int)(k % STAGES);
+                uint32_t ph = (uint32_t)((k / STAGES) & 1);
+                if (k >= STAGES) mbar_wait(&empty[st], ph ^ 1);
+                mbar_expect_tx(&full[st], CHUNK);
+                bulk_g2s(smem + (size_t)st * CHUNK, src + (blockIdx.x + k * gridDim.x) * (size_t)CHUNK, CHUNK, &full[st], pol);
+            }
+        }
+    } else {
+        const int ctid = threadIdx.x;  // 0 .. CW*32-1
+        for (size_t k = 0; k < mine; k++) {
+            int st = (int)(k % STAGES);
+            uint32_t ph = (uint32_t)((k / STAGES) & 1);
+            mbar_wait(&full[st], ph);
+            const ulonglong2 *p = reinterpret_cast<const ulonglong2 *>(smem + (size_t)st * CHUNK);
+#pragma unroll 8
+            for (int i = ctid; i < CHUNK / 16; i += CW * 32) { ulonglong2 v = p[i]; x ^= v.x ^ v.y; s64 += v.x + v.y; }
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&empty[st]);
+        }
+    }
+    if (x == 0x1234567 && s64 == 0x7654321) out[blockIdx.x * blockDim.x + threadIdx.x] = make_ulonglong2(x, s64);
+    if (threadIdx.x == 0 && blockIdx.x == 0) out[0] = make_ulonglong2(x, s64);
+}
+
+// copy via TMA: bulk load to smem, bulk store from smem (no register traffic at all)
+template <int STAGES, int CHUNK>
+__global__ void __launch_bounds__(64, 1) copy_tma(char *__restrict__ dst, const char *__restrict__ src, size_t n_chunks) {
+    extern __shared__ __align__(128) unsigned char smem[];
+    __shared__ uint64_t full[STAGES];
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < STAGES; s++) mbar_init(&full[s], 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+    if (threadIdx.x != 0) return;
+    const size_t mine = n_chunks > blockIdx.x ? (n_chunks - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
+    const uint64_t pol = policy_evict_first();
+    // prologue: fill the ring
+    for (size_t k = 0; k < mine && k < (size_t)STAGES; k++) {
+        mbar_expect_tx(&full[k], CHUNK);
+        bulk_g2s(smem + k * CHUNK, src + (blockIdx.x + k * gridDim.x) * (size_t)CHUNK, CHUNK, &full[k], pol);
+    }
+    for (size_t k = 0; k < mine; k++) {
+        int st = (int)(k % STAGES);
+        uint32_t ph = (uint32_t)((k / STAGES) & 1);
+        mbar_wait(&full[st], ph);
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        bulk_s2g(dst + (blockIdx.x + k * gridDim.x) * (size_t)CHUNK, smem + (size_t)st * CHUNK, CHUNK);
+        asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+        size_t nk = k + STAGES;
+        if (nk < mine) {
+            // the stage can be refilled once its store has finished READING smem
+            asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+            mbar_expect_tx(&full[st], CHUNK);
+            bulk_g2s(smem + (size_t)st * CHUNK, src + (blockIdx.x + nk * gridDim.x) * (size_t)CHUNK, CHUNK, &full[st], pol);
+        }
+    }
+    asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+}
+
+static cudaEvent_t e0, e1;
+template <class F>
+double time_ms(F launch, int warm = 3, int iters = 10) {
+    for (int i = 0; i < warm; i++) launch();
+    CK(cudaDeviceSynchronize());
+    CK(cudaEventRecord(e0));
+    for (int i = 0; i < iters; i++) launch();
+    CK(cudaEventRecord(e1));
+    CK(cudaEventSynchronize(e1));
+    CK(cudaGetLastError());
+    float ms;
+    CK(cudaEventElapsedTime(&ms, e0, e1));
+    return ms / iters;
+}
+
+__global__ void fill(uint64_t *p, size_t n) {
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) p[i] = 0x9E3779B97F4A7C15ull * i;
+}
+
+int main(int argc, char **argv) {
+    size_t bytes = (argc > 1 ? strtoull(argv[1], nullptr, 0) : 4096) << 20;
+    int sms = 0;
+    CK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, 0));
+    char *src, *dst;
+    ulonglong2 *out;
+    CK(cudaMalloc(&src, bytes));
+    CK(cudaMalloc(&dst, bytes));
+    CK(cudaMalloc(&out, sizeof(ulonglong2) * 1024 * 4096));
+    CK(cudaEventCreate(&e0));
+    CK(cudaEventCreate(&e1));
+    fill<<<sms * 8, 512>>>((uint64_t *)src, bytes / 8);
+    CK(cudaDeviceSynchronize());
+    const size_t n16 = bytes / 16;
+    const double gb = bytes / 1e9;
+    printf("sms=%d bytes=%zu\n", sms, bytes);
+
+#define COPY(T, U, BPS, LH, SH, MULT)                                                                            \
+    {                                                                                                            \
+        double ms = time_ms([&] { copy_ldg<T, U, BPS, LH, SH><<<sms * BPS * MULT, T>>>(dst, src, n16); });      \
+        printf("copy  ldg T=%4d U=%2d BPS=%d lh=%d sh=%d grid=%5d : %8.1f GB/s (r+w) %.4f ms\n", T, U, BPS, LH, SH, sms * BPS * MULT, 2 * gb / ms * 1e3, ms); \
+    }
+#define READ(T, U, BPS, HINT, MULT)                                                                              \
+    {                                                                                                            \
+        double ms = time_ms([&] { read_ldg<T, U, BPS, HINT><<<sms * BPS * MULT, T>>>(src, n16, out); });        \
+        printf("read  ldg T=%4d U=%2d BPS=%d hint=%d grid=%5d : %8.1f GB/s  %.4f ms\n", T, U, BPS, HINT, sms * BPS * MULT, gb / ms * 1e3, ms); \
+    }
+    if (argc > 2) {  // second-stage sweep: grid oversubscription
+        for (int mult : {1, 2, 4, 8, 16, 32, 64, 128}) {
+            READ(512, 8, 2, 2, mult)
+            READ(512, 8, 2, 0, mult)
+            READ(256, 16, 2, 2, mult)
+            READ(256, 8, 4, 2, mult)
+            READ(1024, 4, 2, 2, mult)
+        }
+        for (int mult : {1, 2, 4, 8, 16, 32, 64, 128}) {
+            COPY(512, 8, 2, 2, 1, mult)
+            COPY(512, 8, 2, 0, 0, mult)
+            COPY(512, 4, 4, 2, 1, mult)
+            COPY(256, 8, 4, 2, 1, mult)
+            COPY(512, 8, 2, 2, 2, mult)
+        }
+        return 0;
+    }
+    READ(512, 8, 2, 2, 1)
+    READ(512, 8, 2, 2, 16)
+
+#define RTMA(ST, CH, CW)                                                                                         \
+    {                                                                                                            \
+        size_t smem = (size_t)ST * CH;                                                                           \
+        CK(cudaFuncSetAttribute(read_tma<ST, CH, CW>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
+        double ms = time_ms([&] { read_tma<ST, CH, CW><<<sms, (CW + 1) * 32, smem>>>(src, bytes / CH, out); }); \
+        printf("read  tma stages=%d chunk=%6d cw=%2d smem=%6zu        : %8.1f GB/s  %.4f ms\n", ST, CH, CW, smem, gb / ms * 1e3, ms); \
+    }
+    RTMA(4, 32768, 8)
+    RTMA(6, 32768, 8)
+    RTMA(8, 16384, 8)
+    RTMA(12, 16384, 8)
+    RTMA(3, 65536, 8)
+    RTMA(6, 32768, 16)
+    RTMA(13, 16384, 4)
+    RTMA(24, 8192, 8)
+
+    COPY(512, 8, 2, 2, 1, 1)
+    COPY(512, 8, 2, 2, 0, 1)
+    COPY(512, 8, 2, 2, 2, 1)
+    COPY(512, 8, 2, 0, 0, 1)
+    COPY(1024, 4, 2, 2, 1, 1)
+    COPY(512, 4, 4, 2, 1, 1)
+    COPY(256, 8, 4, 2, 1, 1)
+    COPY(512, 4, 2, 2, 1, 1)
+    COPY(256, 4, 8, 2, 1, 1)
+    COPY(512, 8, 2, 2, 1, 8)
+    COPY(512, 2, 4, 2, 1, 1)
+    COPY(1024, 2, 2, 2, 1, 1)
+
+#define CTMA(ST, CH)                                                                                             \
+    {                                                                                                            \
+        size_t smem = (size_t)ST * CH;                                                                           \
+        CK(cudaFuncSetAttribute(copy_tma<ST, CH>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));     \
+        double ms = time_ms([&] { copy_tma<ST, CH><<<sms, 64, smem>>>(dst, src, bytes / CH); });                \
+        printf("copy  tma stages=%d chunk=%6d smem=%6zu              : %8.1f GB/s (r+w) %.4f ms\n", ST, CH, smem, 2 * gb / ms * 1e3, ms); \
+    }
+    CTMA(4, 32768)
+    CTMA(6, 32768)
+    CTMA(8, 16384)
+    CTMA(12, 16384)
+    CTMA(3, 65536)
+    {
+        double ms = time_ms([&] { CK(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToDevice)); });
+        printf("copy  cudaMemcpyAsync D2D                              : %8.1f GB/s (r+w) %.4f ms\n", 2 * gb / ms * 1e3, ms);
+    }
+    // verify the TMA copy actually copied
+    CK(cudaMemset(dst, 0, bytes));
+    {
+        size_t smem = (size_t)6 * 32768;
+        copy_tma<6, 32768><<<sms, 64, smem>>>(dst, src, bytes / 32768);
+        CK(cudaDeviceSynchronize());
+        uint64_t a[4], b[4];
+        size_t offs[2] = {0, bytes - 32};
+        int ok = 1;
+        for (size_t o : offs) {
+            CK(cudaMemcpy(a, src + o, 32, cudaMemcpyDeviceToHost));
+            CK(cudaMemcpy(b, dst + o, 32, cudaMemcpyDeviceToHost));
+            for (int i = 0; i < 4; i++) ok &= a[i] == b[i];
+        }
+        printf("tma copy verify: %s\n", ok ? "ok" : "MISMATCH");
+    }
+    return 0;
+}
