@@ -64,6 +64,74 @@ __global__ void __launch_bounds__(T, BPS) copy_ldg(char *__restrict__ dst, const
     }
 }
 
+// one tile per CTA (grid = tiles), block-reduce, then atomics into 1024 spread slots (must be zeroed beforehand)
+template <int T, int U, int BPS>
+__global__ void __launch_bounds__(T, BPS) read_onetile(const char *__restrict__ src, size_t n16, unsigned long long *slots) {
+    constexpr size_t kTile = (size_t)T * U;
+    const uint64_t pol = policy_evict_first();
+    const char *base = src + (size_t)blockIdx.x * kTile * 16;
+    U2 v[U];
+#pragma unroll
+    for (int j = 0; j < U; j++) v[j] = ld16<2>(base + ((size_t)j * T + threadIdx.x) * 16, pol);
+    uint64_t x = 0, s = 0;
+#pragma unroll
+    for (int j = 0; j < U; j++) { x ^= v[j].a ^ v[j].b; s += v[j].a + v[j].b; }
+    for (int o = 16; o > 0; o >>= 1) { x ^= __shfl_xor_sync(~0u, x, o); s += __shfl_xor_sync(~0u, s, o); }
+    __shared__ uint64_t sx[T / 32], ss[T / 32];
+    if ((threadIdx.x & 31) == 0) { sx[threadIdx.x >> 5] = x; ss[threadIdx.x >> 5] = s; }
+    __syncthreads();
+    if (threadIdx.x < 32) {
+        x = threadIdx.x < T / 32 ? sx[threadIdx.x] : 0;
+        s = threadIdx.x < T / 32 ? ss[threadIdx.x] : 0;
+        for (int o = 16; o > 0; o >>= 1) { x ^= __shfl_xor_sync(~0u, x, o); s += __shfl_xor_sync(~0u, s, o); }
+        if (threadIdx.x == 0) {
+            unsigned slot = blockIdx.x & 1023;
+            atomicXor(&slots[2 * slot], (unsigned long long)x);
+            atomicAdd(&slots[2 * slot + 1], (unsigned long long)s);
+        }
+    }
+}
+
+// persistent CTAs pulling tiles from a global counter (dynamic load balance), next index prefetched one tile ahead
+template <int T, int U, int BPS>
+__global__ void __launch_bounds__(T, BPS) read_dyn(const char *__restrict__ src, size_t n16, ulonglong2 *out, unsigned long long *counter) {
+    constexpr size_t kTile = (size_t)T * U;
+    const size_t tiles = n16 / kTile;
+    const uint64_t pol = policy_evict_first();
+    __shared__ unsigned long long next[2];
+    uint64_t x = 0, s = 0;
+    if (threadIdx.x == 0) next[0] = atomicAdd(counter, 1ull);
+    __syncthreads();
+    int buf = 0;
+    while (true) {
+        unsigned long long t = next[buf];
+        if (t >= tiles) break;
+        if (threadIdx.x == 0) next[buf ^ 1] = atomicAdd(counter, 1ull);
+        const char *base = src + t * kTile * 16;
+        U2 v[U];
+#pragma unroll
+        for (int j = 0; j < U; j++) v[j] = ld16<2>(base + ((size_t)j * T + threadIdx.x) * 16, pol);
+#pragma unroll
+        for (int j = 0; j < U; j++) { x ^= v[j].a ^ v[j].b; s += v[j].a + v[j].b; }
+        __syncthreads();
+        buf ^= 1;
+    }
+    if (x == 0x1234567 && s == 0x7654321) out[blockIdx.x * T + threadIdx.x] = make_ulonglong2(x, s);
+    if (threadIdx.x == 0 && blockIdx.x == 0) out[0] = make_ulonglong2(x, s);
+}
+
+template <int T, int U, int BPS>
+__global__ void __launch_bounds__(T, BPS) copy_onetile(char *__restrict__ dst, const char *__restrict__ src) {
+    constexpr size_t kTile = (size_t)T * U;
+    const uint64_t pol = policy_evict_first();
+    const size_t off = (size_t)blockIdx.x * kTile * 16;
+    U2 v[U];
+#pragma unroll
+    for (int j = 0; j < U; j++) v[j] = ld16<2>(src + off + ((size_t)j * T + threadIdx.x) * 16, pol);
+#pragma unroll
+    for (int j = 0; j < U; j++) st16<1>(dst + off + ((size_t)j * T + threadIdx.x) * 16, v[j], pol);
+}
+
 // ---- TMA bulk (cp.async.bulk, UBLKCP) ring: 1 producer warp + CW consumer warps ------------------------------
 __device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
 __device__ __forceinline__ void mbar_init(uint64_t *b, int count) { asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(b)), "r"(count)); }
@@ -206,6 +274,39 @@ int main(int argc, char **argv) {
     {                                                                                                            \
         double ms = time_ms([&] { read_ldg<T, U, BPS, HINT><<<sms * BPS * MULT, T>>>(src, n16, out); });        \
         printf("read  ldg T=%4d U=%2d BPS=%d hint=%d grid=%5d : %8.1f GB/s  %.4f ms\n", T, U, BPS, HINT, sms * BPS * MULT, gb / ms * 1e3, ms); \
+    }
+    if (argc > 2 && argv[2][0] == '3') {  // third stage: one tile per CTA, and dynamic tile counter
+        unsigned long long *slots;
+        CK(cudaMalloc(&slots, 2048 * 8 + 64));
+        unsigned long long *counter = slots + 2048;
+#define ONE(T, U, BPS)                                                                                           \
+    {                                                                                                            \
+        size_t tiles = n16 / ((size_t)T * U);                                                                    \
+        double ms = time_ms([&] { CK(cudaMemsetAsync(slots, 0, 2048 * 8)); read_onetile<T, U, BPS><<<(unsigned)tiles, T>>>(src, n16, slots); }); \
+        printf("read  onetile T=%4d U=%2d BPS=%d grid=%7zu (+memset+atomics) : %8.1f GB/s  %.4f ms\n", T, U, BPS, tiles, gb / ms * 1e3, ms); \
+    }
+        ONE(512, 8, 2) ONE(512, 4, 4) ONE(256, 8, 4) ONE(256, 16, 2) ONE(1024, 4, 2) ONE(512, 16, 1) ONE(256, 4, 8) ONE(128, 8, 8) ONE(1024, 8, 1) ONE(512, 2, 4)
+#define DYN(T, U, BPS, MULT)                                                                                     \
+    {                                                                                                            \
+        double ms = time_ms([&] { CK(cudaMemsetAsync(counter, 0, 8)); read_dyn<T, U, BPS><<<sms * BPS * MULT, T>>>(src, n16, out, counter); }); \
+        printf("read  dyn     T=%4d U=%2d BPS=%d grid=%7d (+memset)         : %8.1f GB/s  %.4f ms\n", T, U, BPS, sms * BPS * MULT, gb / ms * 1e3, ms); \
+    }
+        DYN(512, 8, 2, 1) DYN(512, 4, 4, 1) DYN(256, 8, 4, 1) DYN(1024, 4, 2, 1) DYN(512, 8, 2, 2) DYN(256, 16, 2, 1) DYN(512, 4, 2, 1) DYN(256, 4, 8, 1)
+#define CONE(T, U, BPS)                                                                                          \
+    {                                                                                                            \
+        size_t tiles = n16 / ((size_t)T * U);                                                                    \
+        double ms = time_ms([&] { copy_onetile<T, U, BPS><<<(unsigned)tiles, T>>>(dst, src); });                 \
+        printf("copy  onetile T=%4d U=%2d BPS=%d grid=%7zu : %8.1f GB/s (r+w) %.4f ms\n", T, U, BPS, tiles, 2 * gb / ms * 1e3, ms); \
+    }
+        CONE(512, 8, 2) CONE(512, 4, 4) CONE(256, 8, 4) CONE(256, 4, 8) CONE(1024, 4, 2) CONE(512, 2, 4) CONE(128, 8, 8) CONE(256, 16, 2) CONE(1024, 2, 2) CONE(256, 2, 8)
+        for (size_t mb : {64, 256, 1024}) {
+            size_t b2 = mb << 20, m16 = b2 / 16;
+            double ms = time_ms([&] { CK(cudaMemsetAsync(slots, 0, 2048 * 8)); read_onetile<512, 8, 2><<<(unsigned)(m16 / 4096), 512>>>(src, m16, slots); });
+            printf("read  onetile %5zu MiB: %8.1f GB/s %.4f ms\n", mb, b2 / 1e9 / ms * 1e3, ms);
+            ms = time_ms([&] { read_ldg<512, 8, 2, 2><<<sms * 2, 512>>>(src, m16, out); });
+            printf("read  persist %5zu MiB: %8.1f GB/s %.4f ms\n", mb, b2 / 1e9 / ms * 1e3, ms);
+        }
+        return 0;
     }
     if (argc > 2) {  // second-stage sweep: grid oversubscription
         for (int mult : {1, 2, 4, 8, 16, 32, 64, 128}) {
