@@ -336,6 +336,74 @@ GFD_API int gfd_hbm_copy(void *d_dst, const void *d_src, size_t bytes, void *str
     return launch_copy(dev, d_dst, d_src, bytes, static_cast<cudaStream_t>(stream), nullptr);
 }
 
+// ---- allocation-free form of the read checksum -----------------------------------------------------------
+//
+// Who this is for.  gfd_hbm_read_checksum needs a scratch buffer, so somebody has to own a device allocation.
+// Some users of this library cannot make one at the moment they want a checksum:
+//   * a health-check or telemetry agent that shares the GPU with a job which has already claimed (nearly) all
+//     of HBM -- a cudaMalloc from the agent can fail, or can push the job itself into an out-of-memory error;
+//   * code that runs inside somebody else's memory pool discipline (a framework that forbids raw cudaMalloc
+//     because it would fragment or bypass its caching allocator);
+//   * code on a path where allocating is not allowed at all, e.g. after a stream has started capturing.
+// For them the per-CTA partial sums live in the fixed array below.  It is part of this library's device image:
+// every GPU on which the library's kernels get loaded carries these 16 KiB from then until the process exits,
+// whether or not this entry point is ever called.
+//
+// Limits and rules (also in include/gfd_b200.h):
+//   * at most GFD_NOALLOC_MAX_BYTES (16 GiB) per call; larger buffers are refused with GFD_ERR_SIZE_LIMIT --
+//     checksum them piecewise (whole 8-byte words per piece) and combine: xor the xor64s, add the sum64s;
+//   * the array has room for 1024 CTAs' partials; a GPU whose launch shape would need more is refused the same way;
+//   * the FIRST call on each GPU looks the array's device address up (cudaGetSymbolAddress), which may make the
+//     driver load this library's kernels on that GPU.  Make that first call early, before any stream capture;
+//   * all calls on one GPU share the one array.  Nothing in it has to start at zero: each launched CTA overwrites
+//     its own slot and the finishing kernel reads exactly the slots of that launch, so stale contents of an earlier
+//     call are never read.  But two calls that run on the GPU at the same time (different streams, or different
+//     host threads) write the same slots and corrupt each other's result: keep calls on one stream, or order them.
+namespace {
+constexpr int kNoAllocMaxBlocks = 1024;
+constexpr size_t kNoAllocMaxBytes = 16ull << 30;
+static __device__ __align__(256) ulonglong2 g_noalloc_partials[kNoAllocMaxBlocks];
+
+// In host code `g_noalloc_partials` is only a handle for the runtime, not an address a kernel can use.
+// The real per-device address is resolved once per GPU, with that GPU current, and cached here.
+void *g_noalloc_addr[kMaxDevices];
+bool g_noalloc_ready[kMaxDevices];
+std::mutex g_noalloc_mu;
+
+int noalloc_scratch(int dev, void **out) {
+    if (dev < 0 || dev >= kMaxDevices) return GFD_ERR_BAD_ARGUMENT;
+    std::lock_guard<std::mutex> lk(g_noalloc_mu);
+    if (!g_noalloc_ready[dev]) {
+        void *p = nullptr;
+        cudaError_t e = cudaGetSymbolAddress(&p, g_noalloc_partials);  // the caller has made `dev` current
+        if (e != cudaSuccess) { (void)cudaGetLastError(); return GFD_ERR_CUDA + (int)e; }
+        if (!p) return GFD_ERR_CUDA + (int)cudaErrorInvalidSymbol;
+        g_noalloc_addr[dev] = p;
+        g_noalloc_ready[dev] = true;
+    }
+    *out = g_noalloc_addr[dev];
+    return 0;
+}
+}  // namespace
+
+GFD_API int gfd_hbm_read_checksum_noalloc(const void *d_buf, size_t bytes, gfd_checksum *d_out, void *stream) {
+    int n, dev;
+    int rc = device_count_checked(&n);
+    if (rc) return rc;
+    if (!d_out || (bytes && !d_buf)) return GFD_ERR_BAD_ARGUMENT;
+    if (bytes > kNoAllocMaxBytes) return GFD_ERR_SIZE_LIMIT;
+    if ((uintptr_t)d_buf % 16 || (uintptr_t)d_out % 8) return GFD_ERR_ALIGNMENT;
+    if ((rc = device_of_pointer(d_out, &dev))) return rc;
+    DeviceScope scope(dev);
+    if (scope.rc) return scope.rc;
+    DevInfo di;
+    if ((rc = device_info(dev, &di))) return rc;
+    if (grid_for(di.sms, bytes / 16) > kNoAllocMaxBlocks) return GFD_ERR_SIZE_LIMIT;
+    void *scratch = nullptr;
+    if ((rc = noalloc_scratch(dev, &scratch))) return rc;
+    return launch_read(dev, d_buf, bytes, d_out, scratch, static_cast<cudaStream_t>(stream), nullptr);
+}
+
 // ---- host-buffer form ---------------------------------------------------------------------------------
 namespace {
 struct Staging {

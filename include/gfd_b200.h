@@ -210,6 +210,21 @@ int gfd_hbm_read_checksum(const void *d_buf, size_t bytes, gfd_checksum *d_out, 
  * peer-mapped address on another GPU (that is the NVLink probe's kernel). */
 int gfd_hbm_copy(void *d_dst, const void *d_src, size_t bytes, void *stream);
 
+/* gfd_hbm_read_checksum without any allocation, by the caller or by the library.  No counterpart in the
+ * reference.  Meant for callers that hold the data on the GPU but must not (or cannot) allocate device memory
+ * when they need the checksum: an agent next to a job that already owns almost all of HBM, code living under a
+ * framework's allocator rules, code past the start of a stream capture.  The per-CTA partial sums go to a fixed
+ * 16 KiB array inside the library's device image (each GPU that loads the library's kernels holds it until exit).
+ *   - bytes <= GFD_NOALLOC_MAX_BYTES, else GFD_ERR_SIZE_LIMIT (split the buffer at 8-byte multiples and combine
+ *     the pieces: xor of xor64, sum of sum64); also GFD_ERR_SIZE_LIMIT on a GPU needing more than 1024 CTAs.
+ *   - the first call on each GPU resolves the array's address and may load the kernels there: do it once at
+ *     start-up, before any stream capture begins.
+ *   - calls on the same GPU share the array; ones that overlap in time on the GPU corrupt each other.  Issue them
+ *     on one stream or serialise them.  Nothing needs clearing between calls.
+ * Same result, bit for bit, as gfd_hbm_read_checksum.  d_buf 16-byte aligned, d_out device memory. */
+#define GFD_NOALLOC_MAX_BYTES (16ull << 30)
+int gfd_hbm_read_checksum_noalloc(const void *d_buf, size_t bytes, gfd_checksum *d_out, void *stream);
+
 /* Host-buffer form (the end-to-end call): copy `bytes` from host memory to GPU `cuda_device`, checksum
  * them there, bring the 16-byte result back.  Staging memory is allocated on first use and cached. */
 int gfd_checksum_host(int cuda_device, const void *host_buf, size_t bytes, gfd_checksum *out);
