@@ -95,6 +95,10 @@ struct gfd_mgr {
     bool attached = false;  // KEEP_ATTACHED: an extra nvmlInit reference is held
     gfd::NvmlApi nv;
     gfd::Cached<std::vector<std::unique_ptr<gfd_dev>>> devices;
+    // Device objects of the previous bracket.  A handle used after gfd_shutdown is a caller bug, but it must get
+    // GFD_ERR_NOT_INITIALIZED (what NVML answers for a stale handle), not a use-after-free: the objects stay
+    // allocated until the next gfd_init or gfd_mgr_free.
+    std::vector<std::unique_ptr<gfd_dev>> retired;
     std::atomic<uint64_t> nvml_calls{0}, dl_probes{0};
     // CUDA (Tegra) backend state lives in gfd_cuda_mgr.cpp
     void *cuda_state = nullptr;

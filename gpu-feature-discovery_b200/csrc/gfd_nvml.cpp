@@ -397,6 +397,7 @@ GFD_API int gfd_init(gfd_mgr *m) {
     m->nvml_calls = 0;
     m->dl_probes = 0;
     m->devices = {};
+    m->retired.clear();
     if (m->backend == GFD_BACKEND_NULL) { m->initialized = true; return 0; }  // null.go:35-37
     if (m->backend == GFD_BACKEND_CUDA) {
         int rc = cuda_mgr_init(m);
@@ -428,7 +429,9 @@ GFD_API int gfd_init(gfd_mgr *m) {
 GFD_API int gfd_shutdown(gfd_mgr *m) {
     if (!m) return GFD_ERR_BAD_ARGUMENT;
     if (!m->initialized) return (m->backend == GFD_BACKEND_NULL) ? 0 : GFD_ERR_NOT_INITIALIZED;
-    m->devices = {};  // handles die with the bracket
+    // handles die with the bracket; their objects are parked so that a stale handle is an error, not a crash
+    for (auto &d : m->devices.v) m->retired.push_back(std::move(d));
+    m->devices = {};
     if (m->backend == GFD_BACKEND_NULL) { m->initialized = false; return 0; }
     if (m->backend == GFD_BACKEND_CUDA) { m->initialized = false; return cuda_mgr_shutdown(m); }
     int rc = NVCALL(m, Shutdown);

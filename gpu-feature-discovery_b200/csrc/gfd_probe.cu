@@ -10,10 +10,14 @@
 //                   NVLink 5 when one side is a peer mapping -- that is the P2P probe's kernel).
 //   fill_pattern    word[i] = 0x9E3779B97F4A7C15 * (i + seed): deterministic, seedless probe input.
 //
-// Shape: persistent grid = SMs x kBlocksPerSM CTAs of kThreads threads; each CTA walks 64 KiB tiles
-// grid-stride; inside a tile every thread issues kUnroll independent 16-byte (or 8 x 32-byte) loads before
-// consuming any (>= 128 KiB in flight per SM, >> HBM latency x bandwidth / 148).  Loads bypass L1
-// (.nc.L1::no_allocate) and are marked evict-first in L2: each byte is touched once.
+// Shape (constants chosen from the on-B200 sweep in profiles/r1_hbm_variant_sweep*.txt):
+//   read: persistent grid = SMs x kBlocksPerSM CTAs of kThreads threads that PULL 64 KiB tiles from a global
+//         counter (a static tile->CTA stride leaves the slower SMs as a tail: 7.2 TB/s; pulling: 7.46 TB/s);
+//         inside a tile every thread issues kUnroll independent 16-byte loads before consuming any
+//         (128 KiB in flight per SM, >> HBM latency x bandwidth / 148).  Loads bypass L1 (.nc.L1::no_allocate)
+//         and are evict-first in L2: each byte is touched once.  256-bit loads measured identical; not used.
+//   copy: one 32 KiB tile per CTA, 1024 threads x 2 vectors, as many CTAs as tiles: the hardware CTA scheduler
+//         does the balancing and short CTAs interleave reads and writes finely (7.06 TB/s r+w vs 5.9 persistent).
 #include <cuda_runtime.h>
 
 #include <cstdio>
@@ -28,7 +32,9 @@ namespace {
 constexpr int kThreads = 512;
 constexpr int kUnroll = 8;             // 16-byte loads in flight per thread
 constexpr int kBlocksPerSM = 2;
-constexpr int kMaxBlocks = 4096;       // scratch is sized for this many partials
+constexpr int kMaxBlocks = 4095;       // scratch = one 16-byte header (tile counter) + this many 16-byte partials
+constexpr int kCopyThreads = 1024;
+constexpr int kCopyUnroll = 2;         // 32 KiB per CTA
 constexpr uint64_t kGolden = 0x9E3779B97F4A7C15ull;
 constexpr int kMaxDevices = 64;
 
@@ -37,7 +43,7 @@ constexpr int kMaxDevices = 64;
 struct U2 { uint64_t a, b; };
 
 // 128-bit streaming load: no L1 allocation, evict-first in L2 through a cache-policy operand (the bare
-// .L2::evict_first qualifier exists only on the 256-bit form below).
+// .L2::evict_first qualifier exists only on the 256-bit ld.global.v4.u64 form).
 __device__ __forceinline__ uint64_t evict_first_policy() {
     uint64_t pol;
     asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
@@ -48,10 +54,6 @@ __device__ __forceinline__ U2 ld_stream16(const void *p, uint64_t pol) {
     asm volatile("ld.global.nc.L1::no_allocate.L2::cache_hint.v2.u64 {%0,%1}, [%2], %3;"
                  : "=l"(r.a), "=l"(r.b) : "l"(p), "l"(pol));
     return r;
-}
-__device__ __forceinline__ void ld_stream32(const void *p, U2 &lo, U2 &hi) {
-    asm volatile("ld.global.nc.L1::no_allocate.L2::evict_first.v4.u64 {%0,%1,%2,%3}, [%4];"
-                 : "=l"(lo.a), "=l"(lo.b), "=l"(hi.a), "=l"(hi.b) : "l"(p));
 }
 __device__ __forceinline__ void st_stream16(void *p, U2 v) {
     asm volatile("st.global.L1::no_allocate.v2.u64 [%0], {%1,%2};" ::"l"(p), "l"(v.a), "l"(v.b) : "memory");
@@ -83,26 +85,30 @@ __device__ __forceinline__ void block_reduce_store(Fold f, ulonglong2 *partials)
 }
 
 // n16 = number of whole 16-byte vectors; the < 16 tail bytes are folded by the finishing kernel.
-template <bool kWide>
+// `tile_counter` must be 0 at launch (the host side clears it on the same stream before every launch).
 __global__ void __launch_bounds__(kThreads, kBlocksPerSM)
-hbm_read_fold_kernel(const char *__restrict__ src, size_t n16, ulonglong2 *__restrict__ partials) {
+hbm_read_fold_kernel(const char *__restrict__ src, size_t n16, unsigned long long *__restrict__ tile_counter,
+                     ulonglong2 *__restrict__ partials) {
     constexpr size_t kTile = (size_t)kThreads * kUnroll;  // 16-byte vectors per tile (64 KiB)
     const size_t full_tiles = n16 / kTile;
     Fold f;
     const uint64_t pol = evict_first_policy();
-    for (size_t t = blockIdx.x; t < full_tiles; t += gridDim.x) {
-        const char *base = src + t * kTile * 16;
+    // Dynamic tile scheduler: thread 0 draws the NEXT tile index while the CTA streams the current one, so the
+    // atomic's round trip hides behind 64 KiB of loads; the two-slot mailbox costs one barrier per tile.
+    __shared__ unsigned long long next_tile[2];
+    if (threadIdx.x == 0) next_tile[0] = atomicAdd(tile_counter, 1ull);
+    __syncthreads();
+    for (int slot = 0;; slot ^= 1) {
+        const unsigned long long t = next_tile[slot];
+        if (t >= full_tiles) break;
+        if (threadIdx.x == 0) next_tile[slot ^ 1] = atomicAdd(tile_counter, 1ull);
+        const char *base = src + (size_t)t * kTile * 16;
         U2 v[kUnroll];
-        if (kWide) {
 #pragma unroll
-            for (int j = 0; j < kUnroll / 2; j++)
-                ld_stream32(base + ((size_t)j * kThreads + threadIdx.x) * 32, v[2 * j], v[2 * j + 1]);
-        } else {
-#pragma unroll
-            for (int j = 0; j < kUnroll; j++) v[j] = ld_stream16(base + ((size_t)j * kThreads + threadIdx.x) * 16, pol);
-        }
+        for (int j = 0; j < kUnroll; j++) v[j] = ld_stream16(base + ((size_t)j * kThreads + threadIdx.x) * 16, pol);
 #pragma unroll
         for (int j = 0; j < kUnroll; j++) f.add(v[j]);
+        __syncthreads();
     }
     // ragged remainder (< one tile), bounds-checked, spread over the whole grid
     for (size_t i = full_tiles * kTile + (size_t)blockIdx.x * kThreads + threadIdx.x; i < n16;
@@ -143,22 +149,21 @@ __global__ void __launch_bounds__(256) fold_finish_kernel(const ulonglong2 *__re
     }
 }
 
-__global__ void __launch_bounds__(kThreads, kBlocksPerSM)
+// One 32 KiB tile per CTA; the last CTA's tile may be partial; CTA 0 also moves the < 16 tail bytes.
+__global__ void __launch_bounds__(kCopyThreads, 2)
 hbm_copy_kernel(char *__restrict__ dst, const char *__restrict__ src, size_t n16, int tail_bytes) {
-    constexpr size_t kTile = (size_t)kThreads * kUnroll;
-    const size_t full_tiles = n16 / kTile;
+    constexpr size_t kTile = (size_t)kCopyThreads * kCopyUnroll;
     const uint64_t pol = evict_first_policy();
-    for (size_t t = blockIdx.x; t < full_tiles; t += gridDim.x) {
-        const size_t off = t * kTile * 16;
-        U2 v[kUnroll];
+    const size_t first = (size_t)blockIdx.x * kTile;
+    if (first + kTile <= n16) {
+        U2 v[kCopyUnroll];
 #pragma unroll
-        for (int j = 0; j < kUnroll; j++) v[j] = ld_stream16(src + off + ((size_t)j * kThreads + threadIdx.x) * 16, pol);
+        for (int j = 0; j < kCopyUnroll; j++) v[j] = ld_stream16(src + (first + (size_t)j * kCopyThreads + threadIdx.x) * 16, pol);
 #pragma unroll
-        for (int j = 0; j < kUnroll; j++) st_stream16(dst + off + ((size_t)j * kThreads + threadIdx.x) * 16, v[j]);
+        for (int j = 0; j < kCopyUnroll; j++) st_stream16(dst + (first + (size_t)j * kCopyThreads + threadIdx.x) * 16, v[j]);
+    } else {
+        for (size_t i = first + threadIdx.x; i < n16; i += kCopyThreads) st_stream16(dst + i * 16, ld_stream16(src + i * 16, pol));
     }
-    for (size_t i = full_tiles * kTile + (size_t)blockIdx.x * kThreads + threadIdx.x; i < n16;
-         i += (size_t)gridDim.x * kThreads)
-        st_stream16(dst + i * 16, ld_stream16(src + i * 16, pol));
     if (blockIdx.x == 0 && threadIdx.x < tail_bytes) dst[n16 * 16 + threadIdx.x] = src[n16 * 16 + threadIdx.x];
 }
 
@@ -235,12 +240,7 @@ int grid_for(int sms, size_t n16) {
     return (int)(want < cap ? want : cap);
 }
 
-bool wide_loads() {  // experiment knob; default chosen from profiles/ 
-    static int v = -1;
-    if (v < 0) { const char *e = getenv("GFD_B200_WIDE_LOADS"); v = e ? atoi(e) : 1; }
-    return v != 0;
-}
-
+// Scratch layout: [0,16) header whose first 8 bytes are the tile counter, then one ulonglong2 partial per CTA.
 int launch_read(int dev, const void *d_buf, size_t bytes, gfd_checksum *d_out, void *d_scratch, cudaStream_t st,
                 int *grid_out) {
     DevInfo di;
@@ -249,12 +249,10 @@ int launch_read(int dev, const void *d_buf, size_t bytes, gfd_checksum *d_out, v
     size_t n16 = bytes / 16;
     int tail = (int)(bytes % 16);
     int grid = grid_for(di.sms, n16);
-    auto *partials = static_cast<ulonglong2 *>(d_scratch);
-    bool wide = wide_loads() && ((uintptr_t)d_buf % 32 == 0);
-    if (wide)
-        hbm_read_fold_kernel<true><<<grid, kThreads, 0, st>>>(static_cast<const char *>(d_buf), n16, partials);
-    else
-        hbm_read_fold_kernel<false><<<grid, kThreads, 0, st>>>(static_cast<const char *>(d_buf), n16, partials);
+    auto *counter = static_cast<unsigned long long *>(d_scratch);
+    auto *partials = reinterpret_cast<ulonglong2 *>(static_cast<char *>(d_scratch) + 16);
+    CUDA_TRY(cudaMemsetAsync(counter, 0, 16, st));  // the scratch keeps the previous launch's counter: clear it
+    hbm_read_fold_kernel<<<grid, kThreads, 0, st>>>(static_cast<const char *>(d_buf), n16, counter, partials);
     CUDA_TRY(cudaGetLastError());
     fold_finish_kernel<<<1, 256, 0, st>>>(partials, grid, static_cast<const unsigned char *>(d_buf) + n16 * 16, tail, d_out);
     CUDA_TRY(cudaGetLastError());
@@ -263,14 +261,15 @@ int launch_read(int dev, const void *d_buf, size_t bytes, gfd_checksum *d_out, v
 }
 
 int launch_copy(int dev, void *d_dst, const void *d_src, size_t bytes, cudaStream_t st, int *grid_out) {
-    DevInfo di;
-    int rc = device_info(dev, &di);
-    if (rc) return rc;
+    (void)dev;
+    constexpr size_t kTile = (size_t)kCopyThreads * kCopyUnroll;
     size_t n16 = bytes / 16;
-    int grid = grid_for(di.sms, n16);
-    hbm_copy_kernel<<<grid, kThreads, 0, st>>>(static_cast<char *>(d_dst), static_cast<const char *>(d_src), n16, (int)(bytes % 16));
+    size_t tiles = (n16 + kTile - 1) / kTile;
+    if (tiles < 1) tiles = 1;
+    if (tiles > 0x7fffffffull) return GFD_ERR_SIZE_LIMIT;  // 64 TiB
+    hbm_copy_kernel<<<(unsigned)tiles, kCopyThreads, 0, st>>>(static_cast<char *>(d_dst), static_cast<const char *>(d_src), n16, (int)(bytes % 16));
     CUDA_TRY(cudaGetLastError());
-    if (grid_out) *grid_out = grid;
+    if (grid_out) *grid_out = (int)tiles;
     return 0;
 }
 
@@ -289,7 +288,7 @@ int launch_fill(int dev, void *d_buf, size_t bytes, uint64_t seed, cudaStream_t 
 
 }  // namespace
 
-GFD_API size_t gfd_hbm_scratch_bytes(void) { return sizeof(ulonglong2) * (size_t)kMaxBlocks; }
+GFD_API size_t gfd_hbm_scratch_bytes(void) { return 16 + sizeof(ulonglong2) * (size_t)kMaxBlocks; }
 
 GFD_API int gfd_cuda_device_count(int *count) {
     if (!count) return GFD_ERR_BAD_ARGUMENT;
@@ -352,13 +351,16 @@ GFD_API int gfd_hbm_copy(void *d_dst, const void *d_src, size_t bytes, void *str
 // Limits and rules (also in include/gfd_b200.h):
 //   * at most GFD_NOALLOC_MAX_BYTES (16 GiB) per call; larger buffers are refused with GFD_ERR_SIZE_LIMIT --
 //     checksum them piecewise (whole 8-byte words per piece) and combine: xor the xor64s, add the sum64s;
-//   * the array has room for 1024 CTAs' partials; a GPU whose launch shape would need more is refused the same way;
+//   * the array has room for 1023 CTAs' partials (plus a 16-byte header); a GPU whose launch shape would need
+//     more is refused the same way;
 //   * the FIRST call on each GPU looks the array's device address up (cudaGetSymbolAddress), which may make the
 //     driver load this library's kernels on that GPU.  Make that first call early, before any stream capture;
-//   * all calls on one GPU share the one array.  Nothing in it has to start at zero: each launched CTA overwrites
-//     its own slot and the finishing kernel reads exactly the slots of that launch, so stale contents of an earlier
-//     call are never read.  But two calls that run on the GPU at the same time (different streams, or different
-//     host threads) write the same slots and corrupt each other's result: keep calls on one stream, or order them.
+//   * all calls on one GPU share the one array and it keeps what the last call left there.  The only part that
+//     must start at zero is the 16-byte header (the tile counter the CTAs draw work from); every call clears it
+//     on the caller's stream before launching.  The partial-sum slots need no clearing: each launched CTA
+//     overwrites its own slot and the finishing kernel reads exactly the slots of that launch.  But two calls
+//     that run on the GPU at the same time (different streams, or different host threads) share the counter and
+//     the slots and corrupt each other's result: keep calls on one stream, or order them.
 namespace {
 constexpr int kNoAllocMaxBlocks = 1024;
 constexpr size_t kNoAllocMaxBytes = 16ull << 30;
@@ -398,7 +400,7 @@ GFD_API int gfd_hbm_read_checksum_noalloc(const void *d_buf, size_t bytes, gfd_c
     if (scope.rc) return scope.rc;
     DevInfo di;
     if ((rc = device_info(dev, &di))) return rc;
-    if (grid_for(di.sms, bytes / 16) > kNoAllocMaxBlocks) return GFD_ERR_SIZE_LIMIT;
+    if (grid_for(di.sms, bytes / 16) > kNoAllocMaxBlocks - 1) return GFD_ERR_SIZE_LIMIT;  // slot 0 is the header
     void *scratch = nullptr;
     if ((rc = noalloc_scratch(dev, &scratch))) return rc;
     return launch_read(dev, d_buf, bytes, d_out, scratch, static_cast<cudaStream_t>(stream), nullptr);
