@@ -22,8 +22,8 @@ file write).  The reference has no GPU compute on this path, so:
                    cannot be built on this image), single-threaded like the reference.  kind = "port".
 
 `--impl reference` times that replay alone (rank 0 only under torchrun) and prints the same line shape.
-N > 1 ("replicas only": the pass is per node, it does not shard): every rank runs the node pass and probes its
-own GPU; ms is the max over ranks, probe GB/s the sum.
+N > 1: the pass is per node and does not shard across ranks, so rank 0 runs it once over all N GPUs (the labeler's own
+per-GPU host threads are the multi-GPU path) while every rank probes its own GPU (replicas); probe GB/s is the sum.
 """
 import argparse
 import ctypes
@@ -178,7 +178,7 @@ def workload_config():
     return {"workload": "BASELINE configs[1]: B200 node, MIG strategy none, --no-timestamp, full label set from the real NVML + "
                         "vGPU sysfs scan + atomic file write; one step = one labeling pass",
             "probe": "opt-in hbm_read_fold, %d MiB per launch (input >> 126 MB L2, so no L2 flush between iterations)" % (PROBE_BYTES >> 20),
-            "parallelism": "replicas only (the pass is per node; probes are per GPU)"}
+            "parallelism": "the pass is per node: rank 0 labels all N GPUs (one host thread per GPU), no collective; probes are per-GPU replicas"}
 
 
 def main():
@@ -216,11 +216,16 @@ def main():
     out_file = os.path.join(tmp, "gfd")
 
     # ---- region A: K labeling passes inside the running labeler (W warm-up passes first) ----------------------
+    # The pass is per NODE (one labeler per node is the deployment: a DaemonSet pod), so with N ranks it is rank 0
+    # that runs it -- once, over all N GPUs, with the labeler's own per-GPU host threads -- while the other ranks
+    # wait at the barrier.  N copies of a node-level daemon hammering one driver would measure contention, not GFD.
     barrier()
-    ms = product_passes(B.BIN_PATH, args.warmup + args.steps, out_file)[args.warmup:]
+    pass_ms, product_text = 0.0, ""
+    if rank == 0:
+        ms = product_passes(B.BIN_PATH, args.warmup + args.steps, out_file)[args.warmup:]
+        pass_ms = sum(ms) / len(ms)
+        product_text = open(out_file).read()
     barrier()
-    pass_ms = sum(ms) / len(ms)
-    product_text = open(out_file).read()
 
     # ---- region B: K launches of the dominant kernel, CUDA events on the launching stream ---------------------
     buf = torch.empty(PROBE_BYTES, dtype=torch.uint8, device=dev)
@@ -249,6 +254,7 @@ def main():
     t_hold = time.time()
     while time.time() - t_hold < 0.5:
         B.hbm_read_checksum(buf.data_ptr(), PROBE_BYTES, d_out.data_ptr(), scratch.data_ptr(), scratch.numel(), stream.cuda_stream)
+        launches += 2
         torch.cuda.synchronize()
     kernel_ms = e0.elapsed_time(e1) / args.steps
     probe_gbps = PROBE_BYTES / (kernel_ms * 1e-3) / 1e9
@@ -258,21 +264,25 @@ def main():
     clocks = sampler.summary()
 
     # ---- e2e: the user-facing call, exec -> exit + read the file back ----------------------------------------
-    e2e = []
-    for i in range(args.warmup + args.steps):
-        dt, data = product_oneshot(B.BIN_PATH, out_file)
-        if i >= args.warmup:
-            e2e.append(dt)
-    e2e_ms = sum(e2e) / len(e2e)
+    e2e_ms = 0.0
+    if rank == 0:
+        e2e = []
+        for i in range(args.warmup + args.steps):
+            dt, data = product_oneshot(B.BIN_PATH, out_file)
+            if i >= args.warmup:
+                e2e.append(dt)
+        e2e_ms = sum(e2e) / len(e2e)
+    barrier()
 
     # host-buffer form of the probe kernel through the C ABI (pinned host memory; copies inside the timed region)
     host_bytes = 1 << 30
     pinned = torch.empty(host_bytes, dtype=torch.uint8).pin_memory()
     pinned.random_(0, 256)
+    reps = 5
     for _ in range(2):
         B.checksum_host(local_rank, pinned.data_ptr(), host_bytes)
+    launches += 2 * (2 + reps)  # gfd_checksum_host = hbm_read_fold + fold_finish per call
     t0 = time.perf_counter()
-    reps = 5
     for _ in range(reps):
         host_sum = B.checksum_host(local_rank, pinned.data_ptr(), host_bytes)
     host_gbps = host_bytes * reps / (time.perf_counter() - t0) / 1e9

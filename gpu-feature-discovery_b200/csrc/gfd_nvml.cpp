@@ -492,14 +492,53 @@ GFD_API int gfd_device_get(gfd_mgr *m, int idx, gfd_dev **dev) {
 
 GFD_API int gfd_prefetch(gfd_mgr *m, int threads) {
     CHECK_MGR(m);
-    if (m->backend != GFD_BACKEND_NVML || threads <= 1) return 0;
-    int rc = enumerate(m);
-    if (rc) return 0;  // reported by gfd_device_count, where the reference would see it
+    if (m->backend != GFD_BACKEND_NVML || threads == 1) return 0;
+    if (threads <= 0) {  // auto: one thread per GPU, bounded by the host and by 16
+        unsigned hw = std::thread::hardware_concurrency();
+        threads = hw ? (int)std::min(hw, 16u) : 8;
+        if (threads < 2) return 0;
+    }
+    std::atomic<size_t> next{0};
+    std::vector<std::thread> pool;
+    if (!m->devices.done) {
+        // Threaded walk.  nvmlDeviceGetHandleByIndex is where the driver attaches a GPU (~8 ms each on B200, measured
+        // in profiles/r1_nvml_phase_timing.txt), so on a multi-GPU node the attach itself is what gets spread over
+        // the threads.  Afterwards the per-index results are folded in index order exactly as the serial walk
+        // (device.go:206-236) would: the first failing index decides the error, skipped models are dropped.
+        unsigned count = 0;
+        int rc = NVCALL(m, DeviceGetCount, &count);
+        if (rc == 0 && count < 2) return 0;  // nothing to spread: leave the (serial) walk to gfd_device_count
+        m->devices.done = true;
+        if (rc) { m->devices.rc = rc; return 0; }  // reported by gfd_device_count, where the reference would see it
+        std::vector<std::unique_ptr<gfd_dev>> slots(count);
+        std::vector<int> handle_rc(count, 0);
+        size_t nt = std::min((size_t)count, (size_t)threads);
+        for (size_t t = 0; t < nt; t++)
+            pool.emplace_back([&] {
+                for (size_t i = next.fetch_add(1); i < count; i = next.fetch_add(1)) {
+                    nvmlDevice_t h = nullptr;
+                    handle_rc[i] = NVCALL(m, DeviceGetHandleByIndex, (unsigned)i, &h);
+                    if (handle_rc[i]) continue;
+                    slots[i].reset(new gfd_dev());
+                    slots[i]->mgr = m;
+                    slots[i]->h = h;
+                    if (q_name_raw(slots[i].get()) == 0 && slots[i]->name.v != "NVIDIA DGX Display") prefetch_one(slots[i].get());
+                }
+            });
+        for (auto &t : pool) t.join();
+        for (unsigned i = 0; i < count; i++) {
+            int e = handle_rc[i] ? handle_rc[i] : slots[i]->name.rc;
+            if (e) { m->devices.v.clear(); m->devices.rc = e; return 0; }
+            if (slots[i]->name.v == "NVIDIA DGX Display") continue;
+            m->devices.v.push_back(std::move(slots[i]));
+        }
+        m->devices.rc = 0;
+        return 0;
+    }
+    if (m->devices.rc) return 0;
     size_t n = m->devices.v.size();
     if (n < 2) return 0;
-    std::atomic<size_t> next{0};
     size_t nt = std::min(n, (size_t)threads);
-    std::vector<std::thread> pool;
     for (size_t t = 0; t < nt; t++)
         pool.emplace_back([&] {
             for (size_t i = next.fetch_add(1); i < n; i = next.fetch_add(1)) prefetch_one(m->devices.v[i].get());

@@ -55,7 +55,7 @@ static const std::vector<FlagDef> &flag_defs() {
          "[b200, opt-in] measure peer-to-peer NVLink bandwidth per GPU pair and add nvidia.com/gpu.probe.nvlink.* labels", true},
         {"probe-size-mib", {}, Kind::Int, "4096", {"GFD_PROBE_SIZE_MIB"}, "[b200, opt-in] probe buffer size in MiB", true},
         {"prefetch-threads", {}, Kind::Int, "0", {"GFD_PREFETCH_THREADS"},
-         "[b200, opt-in] host threads used to query GPUs concurrently (0 = serial)", true},
+         "[b200] host threads used to attach and query GPUs concurrently (0 = one per GPU, 1 = serial); never changes the labels", true},
         {"keep-nvml-attached", {}, Kind::Bool, "false", {"GFD_KEEP_NVML_ATTACHED"},
          "[b200, opt-in] keep NVML initialised between labeling passes instead of re-attaching every pass", true},
         {"timing", {}, Kind::Bool, "false", {"GFD_TIMING"}, "[b200, opt-in] log the wall-clock time of every labeling pass", true},

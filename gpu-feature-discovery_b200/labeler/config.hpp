@@ -59,7 +59,7 @@ struct Config {  // V/spec/config.go:33-38, flags.go:43-72
     bool probe_hbm = false;          // --probe-hbm: emit nvidia.com/gpu.probe.hbm.* labels
     bool probe_nvlink = false;       // --probe-nvlink: emit nvidia.com/gpu.probe.nvlink.* labels
     int64_t probe_bytes = 4ll << 30; // --probe-size-mib
-    int prefetch_threads = 0;        // --prefetch-threads: per-GPU enumeration threads (0 = serial)
+    int prefetch_threads = 0;        // --prefetch-threads: per-GPU attach/query threads (0 = one per GPU, 1 = serial)
     bool keep_nvml_attached = false; // --keep-nvml-attached
     bool timing = false;             // --timing: log per-phase wall-clock of every pass
     int passes = 0;                  // --passes N: exit (keeping the file) after N passes; 0 = daemon

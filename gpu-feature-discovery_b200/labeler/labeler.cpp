@@ -406,7 +406,7 @@ Labels nvml_labels(Manager &mgr, const gfdcfg::Config &config) {
     } guard{mgr};
     Labels out;
     try {
-        if (config.prefetch_threads > 1) mgr.prefetch(config.prefetch_threads);
+        mgr.prefetch(config.prefetch_threads);  // 0 = one host thread per GPU (no-op on 0/1-GPU nodes), 1 = serial
         if (mgr.devices().empty()) return out;
         machine_type_label(out, *config.machine_type_file);
         version_labels(out, mgr);
