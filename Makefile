@@ -57,3 +57,15 @@ clean:
 	rm -f $(LIB) $(BIN) $(FAKE) $(FAKE_NOMIG) $(ORACLE_SO) $(REPLAY)
 
 .PHONY: all clean
+
+# ---- sanitizer build of everything host-side: `make asan`, then
+#      GFD_TEST_BINDIR=build/asan python -m pytest tests/test_cli_parity.py tests/test_cli_flags_and_lifecycle.py
+ASAN_DIR := build/asan
+ASAN_FLAGS := -fsanitize=address,undefined -fno-omit-frame-pointer -g -O1
+asan:
+	@mkdir -p $(ASAN_DIR)
+	$(NVCC) $(GENCODE) -O1 -g -lineinfo -std=c++17 -Iinclude -I$(CSRC) --fmad=false \
+	    -Xcompiler -fPIC,-fvisibility=hidden,-Wall,-Wextra,-ffp-contract=off,-fsanitize=address,-fsanitize=undefined,-fno-omit-frame-pointer \
+	    -shared -cudart static -x cu $(LIB_SRCS) -o $(ASAN_DIR)/libgfd_b200.so -ldl -lpthread -lasan -lubsan
+	/usr/bin/g++ $(CXXFLAGS) $(ASAN_FLAGS) -fPIE $(LABELER_SRCS) -o $(ASAN_DIR)/gpu-feature-discovery -L$(ASAN_DIR) -lgfd_b200 -Wl,-rpath,'$$ORIGIN' -lpthread
+.PHONY: asan

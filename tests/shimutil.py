@@ -67,13 +67,19 @@ class ShimManager(O.Manager):
 
     def init(self):
         self._w(self.m.init)
-        if self.prefetch_threads:
-            self.m.prefetch(self.prefetch_threads)
+        if self.prefetch_threads:  # > 1: that many threads; < 0: auto (one per GPU); 0: no prefetch at all
+            self.m.prefetch(self.prefetch_threads if self.prefetch_threads > 0 else 0)
 
     def shutdown(self): return self._w(self.m.shutdown)
     def get_devices(self): return [ShimDevice(x) for x in self._w(self.m.get_devices)]
     def get_driver_version(self): return self._w(self.m.get_driver_version)
     def get_cuda_driver_version(self): return self._w(self.m.get_cuda_driver_version)
+
+
+def binary_path():
+    """The labeler binary under test; GFD_TEST_BINDIR=build/asan selects the ASan/UBSan build (`make asan`)."""
+    d = os.environ.get("GFD_TEST_BINDIR")
+    return os.path.join(ROOT, d, "gpu-feature-discovery") if d else B.BIN_PATH
 
 
 def run_cli(args, env=None, fake=True, nomig=False, timeout=60):
@@ -85,5 +91,5 @@ def run_cli(args, env=None, fake=True, nomig=False, timeout=60):
     if fake:
         e["LD_LIBRARY_PATH"] = (B.FAKE_NVML_NOMIG_DIR if nomig else B.FAKE_NVML_DIR) + ":" + e.get("LD_LIBRARY_PATH", "")
     e.update(env or {})
-    p = subprocess.run([B.BIN_PATH] + list(args), env=e, capture_output=True, timeout=timeout)
+    p = subprocess.run([binary_path()] + list(args), env=e, capture_output=True, timeout=timeout)
     return p.returncode, p.stdout.decode("utf-8", "surrogateescape"), p.stderr.decode("utf-8", "surrogateescape")

@@ -11,7 +11,7 @@ import time
 import pytest
 
 import nodes as N
-from shimutil import B, run_cli, use_node
+from shimutil import B, binary_path, run_cli, use_node
 
 NODES = N.nodes()
 
@@ -230,7 +230,7 @@ def spawn(tmp_path, args, node="c2_1xB200"):
             del env[k]
     env.update(base_env(tmp_path, node))
     env["LD_LIBRARY_PATH"] = B.FAKE_NVML_DIR + ":" + env.get("LD_LIBRARY_PATH", "")
-    return subprocess.Popen([B.BIN_PATH] + args, env=env, stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True)
+    return subprocess.Popen([binary_path()] + args, env=env, stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True)
 
 
 def wait_for(path, timeout=10.0):
