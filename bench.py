@@ -102,14 +102,16 @@ def parse_timing(stderr):
 
 
 def product_passes(binary, passes, out_file, extra=()):
-    p = subprocess.run([binary, "--passes", str(passes), "--sleep-interval", "0s", "--timing", "--no-timestamp", "--mig-strategy=none",
+    # one extra pass is run and dropped: the LAST pass of a process skips nvmlShutdown (fast exit), so it is
+    # not a steady-state pass and must not flatter the mean
+    p = subprocess.run([binary, "--passes", str(passes + 1), "--sleep-interval", "0s", "--timing", "--no-timestamp", "--mig-strategy=none",
                         "-o", out_file] + list(extra), capture_output=True, text=True, timeout=600)
     if p.returncode != 0:
         raise RuntimeError("gpu-feature-discovery failed:\n" + p.stderr[-2000:])
     ms = parse_timing(p.stderr)
-    if len(ms) != passes:
-        raise RuntimeError("expected %d timing lines, got %d" % (passes, len(ms)))
-    return ms
+    if len(ms) != passes + 1:
+        raise RuntimeError("expected %d timing lines, got %d" % (passes + 1, len(ms)))
+    return ms[:-1]
 
 
 def product_oneshot(binary, out_file):

@@ -394,7 +394,7 @@ std::unique_ptr<Manager> new_manager(const gfdcfg::Config &config) {
 }
 
 // ---- NewNVMLLabeler (internal/lm/nvml.go:29-72) ----------------------------------------------------
-Labels nvml_labels(Manager &mgr, const gfdcfg::Config &config) {
+Labels nvml_labels(Manager &mgr, const gfdcfg::Config &config, bool leave_attached) {
     try {
         mgr.init();
     } catch (const PassError &e) {
@@ -402,8 +402,9 @@ Labels nvml_labels(Manager &mgr, const gfdcfg::Config &config) {
     }
     struct Guard {  // defer manager.Shutdown()
         Manager &m;
-        ~Guard() { m.shutdown(); }
-    } guard{mgr};
+        bool skip;
+        ~Guard() { if (!skip) m.shutdown(); }
+    } guard{mgr, leave_attached};
     Labels out;
     try {
         mgr.prefetch(config.prefetch_threads);  // 0 = one host thread per GPU (no-op on 0/1-GPU nodes), 1 = serial

@@ -10,6 +10,8 @@
 #include <ctime>
 #include <string>
 
+#include <unistd.h>
+
 #include "config.hpp"
 #include "go_compat.hpp"
 #include "labeler.hpp"
@@ -33,6 +35,10 @@ const char *signal_name(int s) {  // syscall.Signal.String()
     default: return "signal";
     }
 }
+
+// Set when the last pass of a --oneshot / --passes run left NVML attached on purpose: start() then leaves the
+// process with _exit() right after the label file is in place instead of paying nvmlShutdown on the way out.
+bool g_fast_exit = false;
 
 // run (main.go:148-210): returns restart; throws gfdlm::PassError on error
 bool run(gfdlm::Manager &mgr, const gfdcfg::Config &config, const sigset_t &sigs) {
@@ -58,7 +64,8 @@ bool run(gfdlm::Manager &mgr, const gfdcfg::Config &config, const sigset_t &sigs
     int passes_done = 0;
     while (true) {
         double t0 = now_ms();
-        gfdlm::Labels nvml = gfdlm::nvml_labels(mgr, config);  // lm.NewLabelers: the eager NVML part
+        const bool last_pass = *config.oneshot || (config.passes > 0 && passes_done + 1 >= config.passes);
+        gfdlm::Labels nvml = gfdlm::nvml_labels(mgr, config, last_pass);  // lm.NewLabelers: the eager NVML part
         double t1 = now_ms();
         gfdlm::Labels labels = timestamp;                      // lm.Merge(timestampLabeler, loopLabelers): later wins
         for (auto &kv : nvml) labels[kv.first] = kv.second;
@@ -82,8 +89,8 @@ bool run(gfdlm::Manager &mgr, const gfdcfg::Config &config, const sigset_t &sigs
         double t3 = now_ms();
         if (config.timing) logf("timing: pass %.3f ms (nvml %.3f, vgpu %.3f, write %.3f)", t3 - t0, t1 - t0, t2 - t1, t3 - t2);
 
-        if (*config.oneshot) return false;
-        if (config.passes > 0 && ++passes_done >= config.passes) return false;
+        if (last_pass) { g_fast_exit = true; return false; }
+        ++passes_done;
 
         logf("Sleeping for %s", gocompat::duration_string(*config.sleep_interval_ns).c_str());
         const int64_t ns = *config.sleep_interval_ns < 0 ? 0 : *config.sleep_interval_ns;
@@ -137,7 +144,14 @@ int start(const gfdcfg::ParsedFlags &flags) {
             logf("Error: %s", e.what());
             return 1;
         }
-        if (!restart) return 0;
+        if (!restart) {
+            if (g_fast_exit) {  // the labels are written; the kernel closes the driver handles faster than nvmlShutdown does
+                logf("Exiting");
+                fflush(nullptr);
+                _exit(0);
+            }
+            return 0;
+        }
     }
 }
 
