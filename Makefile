@@ -16,13 +16,14 @@ LIB       := $(PKG)/libgfd_b200.so
 BIN       := $(PKG)/gpu-feature-discovery
 FAKE      := $(PKG)/fake_nvml/lib/libnvidia-ml.so.1
 FAKE_NOMIG:= $(PKG)/fake_nvml/lib_nomig/libnvidia-ml.so.1
+FAKE_CUDA := $(PKG)/fake_cuda/lib/libcuda.so.1
 ORACLE_SO := oracle/libgfd_oracle_c.so
 REPLAY    := oracle/ref_replay
 
 LIB_SRCS  := $(CSRC)/gfd_nvml.cpp $(CSRC)/gfd_mig_profile.cpp $(CSRC)/gfd_cuda_mgr.cpp $(CSRC)/gfd_probe.cu
 LABELER_SRCS := $(wildcard $(PKG)/labeler/*.cpp)
 
-TARGETS := $(LIB) $(FAKE) $(FAKE_NOMIG) $(ORACLE_SO)
+TARGETS := $(LIB) $(FAKE) $(FAKE_NOMIG) $(FAKE_CUDA) $(ORACLE_SO)
 ifneq ($(wildcard oracle/ref_replay.c),)
 TARGETS += $(REPLAY)
 endif
@@ -44,6 +45,10 @@ $(FAKE_NOMIG): $(PKG)/fake_nvml/fake_nvml.c
 	@mkdir -p $(dir $@)
 	$(CC) -O2 -Wall -Wextra -fPIC -shared -fvisibility=hidden -Wl,-soname,libnvidia-ml.so.1 -DFAKE_NO_MIG_SYMBOLS -I$(CUDA_INC) -o $@ $< -lpthread
 
+$(FAKE_CUDA): $(PKG)/fake_cuda/fake_cuda.c
+	@mkdir -p $(dir $@)
+	$(CC) -O2 -Wall -Wextra -fPIC -shared -fvisibility=hidden -Wl,-soname,libcuda.so.1 -o $@ $<
+
 $(ORACLE_SO): oracle/checksum_oracle.c
 	$(CC) -O2 -Wall -Wextra -fPIC -shared -o $@ $<
 
@@ -54,7 +59,7 @@ $(BIN): $(LABELER_SRCS) $(LIB) include/gfd_b200.h
 	$(CXX) $(CXXFLAGS) -fPIE $(LABELER_SRCS) -o $@ -L$(PKG) -lgfd_b200 -Wl,-rpath,'$$ORIGIN' -lpthread
 
 clean:
-	rm -f $(LIB) $(BIN) $(FAKE) $(FAKE_NOMIG) $(ORACLE_SO) $(REPLAY)
+	rm -f $(LIB) $(BIN) $(FAKE) $(FAKE_NOMIG) $(FAKE_CUDA) $(ORACLE_SO) $(REPLAY)
 
 .PHONY: all clean
 

@@ -379,7 +379,8 @@ std::unique_ptr<Manager> new_manager(const gfdcfg::Config &config) {
     char reason[1024];
     bool has_nvml = gfd_has_nvml(reason, sizeof reason) != 0;
     logf("Detected %sNVML platform: %s", has_nvml ? "" : "non-", reason);
-    bool is_tegra = gfd_is_tegra_system("", reason, sizeof reason) != 0;
+    const char *tegra_root = getenv("GFD_B200_TEGRA_ROOT");  // test hook: prefix for the two Tegra probe paths
+    bool is_tegra = gfd_is_tegra_system(tegra_root ? tegra_root : "", reason, sizeof reason) != 0;
     logf("Detected %sTegra platform: %s", is_tegra ? "" : "non-", reason);
     if (has_nvml && is_tegra) {
         logf("WARNING: Disabling Tegra-based resources on NVML system");

@@ -232,6 +232,76 @@ class FallbackManager(Manager):
     def get_driver_version(self): return self.wraps.get_driver_version()
 
 
+class CudaDevice(Device):
+    """internal/resource/cuda-device.go:25-98 over internal/cuda/api.go.  `raw` = a raw CUDA-driver object whose methods
+    return (CUresult, value): oracle/nvml_model.py:RawCuda."""
+
+    def __init__(self, raw, ordinal):
+        self.raw, self.d = raw, ordinal
+
+    def get_attributes(self): raise GfdError("GetAttributes is not supported for CUDA devices")
+    def get_device_handle_from_mig_device_handle(self): raise GfdError("GetDeviceHandleFromMigDeviceHandle is unsupported for CUDA devices")
+    def get_mig_devices(self): raise GfdError("GetMigDevices is unsupported for CUDA devices")
+    def is_mig_capable(self): return False
+    def is_mig_enabled(self): return False
+
+    def get_cuda_compute_capability(self):
+        r, major = self.raw.device_get_attribute(75, self.d)
+        if r:
+            raise GfdError("failed to get CUDA compute capability major for device: result=%d" % r)
+        r, minor = self.raw.device_get_attribute(76, self.d)
+        if r:
+            raise GfdError("failed to get CUDA compute capability minor for device: result=%d" % r)
+        return major, minor
+
+    def get_total_memory_mb(self):
+        r, total = self.raw.device_total_mem(self.d)
+        if r:
+            raise GfdError("failed to get memory info for device: %d" % r)
+        return total // (1024 * 1024)
+
+    def get_name(self):
+        r, name = self.raw.device_get_name(self.d)
+        if r:
+            raise GfdError("failed to get device name: %d" % r)
+        return name
+
+
+class CudaManager(Manager):
+    """internal/resource/cuda-lib.go:25-88 (Tegra: no NVML, libcuda only)."""
+
+    def __init__(self, raw):
+        self.raw = raw
+
+    def init(self):
+        r, _ = self.raw.init()
+        if r:
+            raise GfdError("%d" % r)
+
+    def shutdown(self): return None
+
+    def get_devices(self):
+        r, count = self.raw.device_get_count()
+        if r:
+            raise GfdError("failed to get number of CUDA devices: %d" % r)
+        out = []
+        for i in range(count):
+            r, d = self.raw.device_get(i)
+            if r:
+                raise GfdError("failed to get CUDA device %d: %d" % (i, r))
+            out.append(CudaDevice(self.raw, d))
+        return out
+
+    def get_cuda_driver_version(self):
+        r, v = self.raw.driver_get_version()
+        if r:
+            raise GfdError("failed to get driver version: %d" % r)
+        return v // 1000, v % 100 // 10  # cuda-lib.go:59-60: `% 100`, unlike the NVML manager's `% 1000`
+
+    def get_driver_version(self):
+        return "unknown.unknown.unknown"  # cuda-lib.go:66-68
+
+
 def with_config(manager, config):
     """internal/resource/factory.go:33-39"""
     if config.fail_on_init_error:

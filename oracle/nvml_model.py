@@ -504,3 +504,45 @@ class PynvmlRaw:
         rc, v = self._call("nvmlGpuInstanceGetComputeInstanceProfileInfo",
                            self.nv.nvmlGpuInstanceGetComputeInstanceProfileInfo, gi, idx, eng)
         return rc, ({"id": int(v.id), "slice_count": int(v.sliceCount)} if rc == 0 else None)
+
+
+# ----------------------------------------------------------------------------
+# RawCuda: the fixture interpreter for the Tegra path (must agree with fake_cuda/fake_cuda.c)
+# ----------------------------------------------------------------------------
+class RawCuda:
+    """devices: list of (total_bytes, cc_major, cc_minor, name).  Every method returns (CUresult, value)."""
+
+    def __init__(self, devices=(), version=12040, rc=None):
+        self.devices, self.version, self.rc = list(devices), version, dict(rc or {})
+
+    def dumps(self):
+        out = ["version %d" % self.version] + ["rc %s %d" % kv for kv in sorted(self.rc.items())]
+        out += ["device %d %d %d %s" % d for d in self.devices]
+        return "\n".join(out) + "\n"
+
+    def _rc(self, sym): return self.rc.get(sym, 0)
+    def init(self): return self._rc("cuInit"), None
+    def driver_get_version(self): return self._rc("cuDriverGetVersion"), self.version
+    def device_get_count(self): return self._rc("cuDeviceGetCount"), len(self.devices)
+
+    def device_get(self, i):
+        r = self._rc("cuDeviceGet")
+        if r:
+            return r, None
+        return (0, i) if 0 <= i < len(self.devices) else (101, None)
+
+    def device_get_attribute(self, attr, d):
+        r = self._rc("cuDeviceGetAttribute")
+        if r:
+            return r, None
+        return 0, {75: self.devices[d][1], 76: self.devices[d][2]}.get(attr, 0)
+
+    def device_total_mem(self, d):
+        # the reference binds the legacy unversioned cuDeviceTotalMem (32-bit out-parameter) into a zeroed uint64
+        # (internal/cuda/cuda.go:108, api.go:107-112): modelled as the low 32 bits.  Parity unpinned (no Tegra here).
+        r = self._rc("cuDeviceTotalMem")
+        return (r, None) if r else (0, self.devices[d][0] & 0xFFFFFFFF)
+
+    def device_get_name(self, d):
+        r = self._rc("cuDeviceGetName")
+        return (r, None) if r else (0, self.devices[d][3][:95])
