@@ -107,7 +107,8 @@ struct gfd_mgr {
 namespace gfd {
 int copy_out(const std::string &s, char *buf, size_t len);
 // implemented in gfd_mig_profile.cpp
-int mig_profile_string(int gi_profile_id, int ci_profile_id, uint64_t mig_mb, uint64_t dev_bytes, std::string *out);
+int mig_profile_string(int gi_profile_id, int ci_profile_id, uint64_t mig_mb, uint64_t dev_bytes, std::string *out,
+                       bool current_tables = false);
 // implemented in gfd_cuda_mgr.cpp
 int cuda_mgr_init(gfd_mgr *m);
 int cuda_mgr_shutdown(gfd_mgr *m);

@@ -38,14 +38,35 @@ static int ci_slices(int id) {
     }
 }
 
-int mig_profile_string(int gi_profile_id, int ci_profile_id, uint64_t mig_mb, uint64_t dev_bytes, std::string *out) {
+// NEW, opt-in (GFD_MGR_CURRENT_TABLES): the GI/CI profile ids the CUDA 12.9 nvml.h adds after the reference's header
+// was cut (nvml.h: NVML_GPU_INSTANCE_PROFILE_2_SLICE_REV1 .. _2_SLICE_ALL_ME, NVML_COMPUTE_INSTANCE_PROFILE_1_SLICE_REV1).
+// Suffixes follow nvidia-smi's profile names: +me, +gfx, -me, +me.all.  No reference counterpart, no parity claim.
+static int gi_slices_current(int id, const char **suffix) {
+    *suffix = "";
+    switch (id) {
+    case 0x8: *suffix = "+me"; return 2;
+    case 0x9: return 1;  // 1 slice with twice the memory: the GB figure already tells them apart (B200 1g.45gb)
+    case 0xA: *suffix = "+gfx"; return 1;
+    case 0xB: *suffix = "+gfx"; return 2;
+    case 0xC: *suffix = "+gfx"; return 4;
+    case 0xD: *suffix = "-me"; return 1;
+    case 0xE: *suffix = "-me"; return 2;
+    case 0xF: *suffix = "+me.all"; return 1;
+    case 0x10: *suffix = "+me.all"; return 2;
+    default: return 0;
+    }
+}
+
+int mig_profile_string(int gi_profile_id, int ci_profile_id, uint64_t mig_mb, uint64_t dev_bytes, std::string *out, bool current_tables) {
+    const char *suffix = (gi_profile_id == 7) ? "+me" : "";
     int g = gi_slices(gi_profile_id);
+    if (!g && current_tables) g = gi_slices_current(gi_profile_id, &suffix);
     if (!g) return GFD_ERR_INVALID_GI_PROFILE;
     int c = ci_slices(ci_profile_id);
+    if (!c && current_tables && ci_profile_id == 7) c = 1;  // NVML_COMPUTE_INSTANCE_PROFILE_1_SLICE_REV1
     if (!c) return GFD_ERR_INVALID_CI_PROFILE;
     // Go: GB: int(getMigMemorySizeGB(...)) printed with %d
     long long gb = (long long)gfd_mig_memory_size_gb(dev_bytes, mig_mb);
-    const char *suffix = (gi_profile_id == 7) ? "+me" : "";
     char buf[96];
     if (c == g)
         snprintf(buf, sizeof buf, "%dg.%lldgb%s", g, gb, suffix);

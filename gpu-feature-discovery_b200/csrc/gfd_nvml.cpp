@@ -237,7 +237,10 @@ int q_mig_profile_name(gfd_dev *m) {
 
     // The reference's NVML 11.x header bounds: ids >= 8 (e.g. B200 1g.45gb = 9) are never probed, so such
     // a device ends in "no matching profile IDs found" -- reproduced on purpose (SURVEY.md Fact 4).
-    const unsigned kGiProfileCount = 8, kCiProfileCount = 7;  // V/go-nvml/nvml/const.go:555,571
+    // GFD_MGR_CURRENT_TABLES (new, opt-in) widens the bounds to the CUDA 12.9 header (0x11 GI / 8 CI profiles).
+    const bool current = (g->flags & GFD_MGR_CURRENT_TABLES) != 0;
+    const unsigned kGiProfileCount = current ? NVML_GPU_INSTANCE_PROFILE_COUNT : 8;      // V/go-nvml/nvml/const.go:555
+    const unsigned kCiProfileCount = current ? NVML_COMPUTE_INSTANCE_PROFILE_COUNT : 7;  // const.go:571
     for (unsigned i = 0; i < kGiProfileCount; i++) {
         Cached<unsigned> &gp = p->gi_profile_info_id[i];
         if (!gp.done) {
@@ -264,7 +267,7 @@ int q_mig_profile_name(gfd_dev *m) {
             if (cp.v != ci_info.profileId) continue;
             std::string prof;
             // NB the loop INDICES (i, j), not the ids, are what the reference feeds NewMigProfile (mig_device.go:136)
-            if ((rc = mig_profile_string((int)i, (int)j, m->attrs.v.memorySizeMB, p->mem_total_bytes.v, &prof))) return fail(rc);
+            if ((rc = mig_profile_string((int)i, (int)j, m->attrs.v.memorySizeMB, p->mem_total_bytes.v, &prof, current))) return fail(rc);
             for (char &c : prof)
                 if (c == '+') c = '.';  // strings.ReplaceAll(p.String(), "+", ".")
             m->name.v = prof;

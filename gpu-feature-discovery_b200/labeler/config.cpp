@@ -58,6 +58,8 @@ static const std::vector<FlagDef> &flag_defs() {
          "[b200] host threads used to attach and query GPUs concurrently (0 = one per GPU, 1 = serial); never changes the labels", true},
         {"keep-nvml-attached", {}, Kind::Bool, "false", {"GFD_KEEP_NVML_ATTACHED"},
          "[b200, opt-in] keep NVML initialised between labeling passes instead of re-attaching every pass", true},
+        {"current-tables", {}, Kind::Bool, "false", {"GFD_CURRENT_TABLES"},
+         "[b200, opt-in] use up-to-date tables where the reference's are stale: gpu.family=blackwell for compute 10.x/12.x, MIG profile ids of CUDA 12.9 (e.g. 1g.45gb) resolved instead of failing; CHANGES labels", true},
         {"timing", {}, Kind::Bool, "false", {"GFD_TIMING"}, "[b200, opt-in] log the wall-clock time of every labeling pass", true},
         {"passes", {}, Kind::Int, "0", {"GFD_PASSES"},
          "[b200, opt-in] label this many times (sleeping --sleep-interval in between), keep the file and exit; 0 = run until signalled", true},
@@ -585,6 +587,7 @@ Config load_config(const ParsedFlags &f) {
     c.prefetch_threads = (int)strtoll(f.str("prefetch-threads").c_str(), nullptr, 0);
     c.keep_nvml_attached = f.boolean("keep-nvml-attached");
     c.timing = f.boolean("timing");
+    c.current_tables = f.boolean("current-tables");
     c.passes = (int)strtoll(f.str("passes").c_str(), nullptr, 0);
     if (const char *root = getenv("GFD_B200_PCI_DEVICES_ROOT")) c.pci_devices_root = root;
     return c;

@@ -61,6 +61,7 @@ struct Config {  // V/spec/config.go:33-38, flags.go:43-72
     int64_t probe_bytes = 4ll << 30; // --probe-size-mib
     int prefetch_threads = 0;        // --prefetch-threads: per-GPU attach/query threads (0 = one per GPU, 1 = serial)
     bool keep_nvml_attached = false; // --keep-nvml-attached
+    bool current_tables = false;     // --current-tables: blackwell family + CUDA 12.9 MIG profile ids (changes labels)
     bool timing = false;             // --timing: log per-phase wall-clock of every pass
     int passes = 0;                  // --passes N: exit (keeping the file) after N passes; 0 = daemon
     std::string pci_devices_root = "/sys/bus/pci/devices";  // GFD_B200_PCI_DEVICES_ROOT (test hook)

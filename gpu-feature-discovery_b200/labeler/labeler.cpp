@@ -23,6 +23,7 @@ namespace gfdlm {
 namespace {
 
 const char *kFullGpuResource = "nvidia.com/gpu";  // internal/lm/resource.go:27
+bool g_current_tables = false;                      // --current-tables (opt-in), set per pass by nvml_labels
 
 [[noreturn]] void fail(const std::string &what, int status) {
     throw PassError(what + ": " + gfd_strerror(status));
@@ -119,7 +120,9 @@ struct ResourceLabeler {
 };
 
 // getArchFamily (resource.go:261-284): the reference's table ends at hopper; anything newer is "undefined"
-const char *arch_family(int major, int minor) {
+const char *arch_family(int major, int minor, bool current_tables) {
+    if (current_tables && (major == 10 || major == 12)) return "blackwell";  // NEW, opt-in (--current-tables)
+    if (current_tables && major == 8 && minor == 9) return "ada-lovelace";  // same name newer GFD releases use
     switch (major) {
     case 1: return "tesla";
     case 2: return "fermi";
@@ -145,7 +148,7 @@ void gpu_resource_labels(Labels &out, const gfdcfg::Config *config, gfd_dev *dev
     rl.base(out, count, {model});
     if (total_mb != 0) out[rl.key("memory")] = std::to_string(total_mb);
     if (major != 0) {  // newArchitectureLabels (resource.go:239-258)
-        out[rl.key("family")] = arch_family(major, minor);
+        out[rl.key("family")] = arch_family(major, minor, g_current_tables);
         out[rl.key("compute.major")] = std::to_string(major);
         out[rl.key("compute.minor")] = std::to_string(minor);
     }
@@ -390,7 +393,7 @@ std::unique_ptr<Manager> new_manager(const gfdcfg::Config &config) {
     if (has_nvml) { logf("Using NVML manager"); backend = GFD_BACKEND_NVML; }
     else if (is_tegra) { logf("Using CUDA manager"); backend = GFD_BACKEND_CUDA; }
     else { logf("WARNING: No valid resources detected; using empty manager."); backend = GFD_BACKEND_NULL; }
-    unsigned flags = config.keep_nvml_attached ? GFD_MGR_KEEP_ATTACHED : 0;
+    unsigned flags = (config.keep_nvml_attached ? GFD_MGR_KEEP_ATTACHED : 0) | (config.current_tables ? GFD_MGR_CURRENT_TABLES : 0);
     return std::unique_ptr<Manager>(new Manager(backend, flags, !*config.fail_on_init_error));  // WithConfig (factory.go:33-39)
 }
 
@@ -407,6 +410,7 @@ Labels nvml_labels(Manager &mgr, const gfdcfg::Config &config, bool leave_attach
         ~Guard() { if (!skip) m.shutdown(); }
     } guard{mgr, leave_attached};
     Labels out;
+    g_current_tables = config.current_tables;
     try {
         mgr.prefetch(config.prefetch_threads);  // 0 = one host thread per GPU (no-op on 0/1-GPU nodes), 1 = serial
         if (mgr.devices().empty()) return out;

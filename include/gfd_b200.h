@@ -88,6 +88,10 @@ enum gfd_backend {
 #define GFD_MGR_KEEP_ATTACHED 0x1u /* hold one extra nvmlInit reference for the manager's lifetime so that
                                       every pass after the first skips the driver attach (new; opt-in) */
 
+#define GFD_MGR_CURRENT_TABLES 0x2u /* resolve MIG GI/CI profile ids beyond the reference's NVML 11.x header (ids up to
+                                      0x10 / 7 of the CUDA 12.9 nvml.h, e.g. B200 1g.45gb) instead of failing with
+                                      "no matching profile IDs found" (new; opt-in; no parity claim) */
+
 int gfd_mgr_new(int backend, unsigned flags, gfd_mgr **out); /* replaces resource.NewManager's backend pick */
 void gfd_mgr_free(gfd_mgr *m);
 

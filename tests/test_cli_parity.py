@@ -244,3 +244,29 @@ def test_missing_pci_root_fails(tmp_path):
 def test_nvidia_function_without_class_file_fails(tmp_path):
     want, rc, got, stderr = vgpu_case(tmp_path, {"0000:5e:00.0": ("0x10de", None, bytes(256))})
     assert want is None and rc == 1
+
+
+# ---- --current-tables (NEW, opt-in): the only flag that changes reference labels, and only when given ---------------
+def test_current_tables_is_opt_in_and_resolves_new_mig_profiles(tmp_path):
+    node = NODES["gi_profile_id_9_fails"]  # B200 1g.45gb: GI profile id 9, beyond the reference's NVML 11.x header
+    rc, got, stderr, _ = cli_pass(tmp_path, node, "mixed")
+    assert rc == 1 and got is None and "no matching profile IDs found" in stderr          # default = the reference's failure
+    rc, got, stderr, _ = cli_pass(tmp_path, node, "mixed", extra_args=["--current-tables"])
+    assert rc == 0, stderr
+    assert "nvidia.com/mig-1g.45gb.count=1\n" in got and "nvidia.com/mig-1g.45gb.product=NVIDIA-B200-MIG-1g.45gb\n" in got
+    assert "nvidia.com/gpu.family=blackwell\n" in got
+    # on a node the reference handles, the flag changes nothing but the family label
+    want, _ = oracle_pass(NODES["c5_mixed_hetero"], "mixed")
+    rc, got, stderr, _ = cli_pass(tmp_path, NODES["c5_mixed_hetero"], "mixed", extra_args=["--current-tables"])
+    assert rc == 0 and got == want.replace("gpu.family=undefined", "gpu.family=blackwell"), stderr
+
+
+def test_current_tables_profile_names():
+    MIBS = 183359 * 1024 * 1024
+    cases = {(8, 1): "2g.45gb+me", (9, 0): "1g.45gb", (0xA, 0): "1g.23gb+gfx", (0xB, 1): "2g.45gb+gfx", (0xC, 3): "4g.90gb+gfx",
+             (0xD, 0): "1g.23gb-me", (0xE, 0): "1c.2g.45gb-me", (0xF, 7): "1g.23gb+me.all", (0x10, 1): "2g.45gb+me.all"}
+    import ctypes
+    for (gi, ci), want in cases.items():
+        mb = {1: 22912, 2: 45824, 4: 91648}[int(want.split("g.")[0][-1])] if "1g.45gb" not in want else 45824
+        with pytest.raises(B.GfdError):
+            B.mig_profile_string(gi, ci, mb, MIBS)  # the plain C-ABI call keeps the reference's tables
