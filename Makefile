@@ -10,7 +10,7 @@ CSRC      := $(PKG)/csrc
 GENCODE   := -gencode arch=compute_100a,code=sm_100a
 NVCCFLAGS := $(GENCODE) -O3 -lineinfo -std=c++17 -Iinclude -I$(CSRC) --fmad=false \
              -Xcompiler -fPIC,-fvisibility=hidden,-Wall,-Wextra,-ffp-contract=off -Xptxas -v
-CXXFLAGS  := -O2 -std=c++17 -Wall -Wextra -fPIC -Iinclude -ffp-contract=off
+CXXFLAGS  := -O2 -std=c++17 -Wall -Wextra -fPIC -Iinclude -ffp-contract=off -ffunction-sections -fdata-sections
 
 LIB       := $(PKG)/libgfd_b200.so
 BIN       := $(PKG)/gpu-feature-discovery
@@ -55,8 +55,11 @@ $(ORACLE_SO): oracle/checksum_oracle.c
 $(REPLAY): oracle/ref_replay.c
 	$(CC) -O2 -Wall -Wextra -I$(CUDA_INC) -o $@ $< -ldl -lm
 
-$(BIN): $(LABELER_SRCS) $(LIB) include/gfd_b200.h
-	$(CXX) $(CXXFLAGS) -fPIE $(LABELER_SRCS) -o $@ -L$(PKG) -lgfd_b200 -Wl,-rpath,'$$ORIGIN' -lpthread
+# The labeler links the HOST-ONLY translation units of the C ABI in statically (same sources as the .so) and dlopen()s
+# libgfd_b200.so only for the opt-in probes (labeler/probe_loader.cpp): no CUDA start-up cost on the default pass.
+CORE_SRCS := $(CSRC)/gfd_nvml.cpp $(CSRC)/gfd_mig_profile.cpp $(CSRC)/gfd_cuda_mgr.cpp
+$(BIN): $(LABELER_SRCS) $(CORE_SRCS) $(CSRC)/gfd_internal.h $(LIB) include/gfd_b200.h $(wildcard $(PKG)/labeler/*.hpp)
+	$(CXX) $(CXXFLAGS) -fPIE -I$(CSRC) -I$(CUDA_INC) $(LABELER_SRCS) $(CORE_SRCS) -o $@ -static-libstdc++ -static-libgcc -Wl,--gc-sections -s -ldl -lpthread
 
 clean:
 	rm -f $(LIB) $(BIN) $(FAKE) $(FAKE_NOMIG) $(FAKE_CUDA) $(ORACLE_SO) $(REPLAY)
@@ -72,5 +75,5 @@ asan:
 	$(NVCC) $(GENCODE) -O1 -g -lineinfo -std=c++17 -Iinclude -I$(CSRC) --fmad=false \
 	    -Xcompiler -fPIC,-fvisibility=hidden,-Wall,-Wextra,-ffp-contract=off,-fsanitize=address,-fsanitize=undefined,-fno-omit-frame-pointer \
 	    -shared -cudart static -x cu $(LIB_SRCS) -o $(ASAN_DIR)/libgfd_b200.so -ldl -lpthread -lasan -lubsan
-	/usr/bin/g++ $(CXXFLAGS) $(ASAN_FLAGS) -fPIE $(LABELER_SRCS) -o $(ASAN_DIR)/gpu-feature-discovery -L$(ASAN_DIR) -lgfd_b200 -Wl,-rpath,'$$ORIGIN' -lpthread
+	/usr/bin/g++ $(CXXFLAGS) $(ASAN_FLAGS) -fPIE -I$(CSRC) -I$(CUDA_INC) $(LABELER_SRCS) $(CORE_SRCS) -o $(ASAN_DIR)/gpu-feature-discovery -ldl -lpthread
 .PHONY: asan

@@ -176,6 +176,21 @@ def reference_arm(args, rank, world):
     return 0
 
 
+def reduce_over_ranks(pass_ms, e2e_ms, kernel_ms, probe_gbps, host_gbps, world, device):
+    """Times: MAX over ranks (the node pass runs on rank 0 only, the others contribute 0).  Probe bandwidths: SUM over
+    ranks (one GPU each).  No data-path collective exists; this is result plumbing (NCCL on GPUs, gloo in the CPU test)."""
+    if world <= 1:
+        return pass_ms, e2e_ms, kernel_ms, probe_gbps, host_gbps
+    import torch
+    import torch.distributed as dist
+    t = torch.tensor([pass_ms, e2e_ms, kernel_ms], device=device, dtype=torch.float64)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    g = torch.tensor([probe_gbps, host_gbps], device=device, dtype=torch.float64)
+    dist.all_reduce(g, op=dist.ReduceOp.SUM)
+    a, b = [float(x) for x in t.cpu()], [float(x) for x in g.cpu()]
+    return a[0], a[1], a[2], b[0], b[1]
+
+
 def workload_config():
     return {"workload": "BASELINE configs[1]: B200 node, MIG strategy none, --no-timestamp, full label set from the real NVML + "
                         "vGPU sysfs scan + atomic file write; one step = one labeling pass",
@@ -290,15 +305,8 @@ def main():
     host_gbps = host_bytes * reps / (time.perf_counter() - t0) / 1e9
 
     # ---- reductions over ranks --------------------------------------------------------------------------------
-    if world > 1:
-        t = torch.tensor([pass_ms, e2e_ms, kernel_ms], device=dev, dtype=torch.float64)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        pass_ms, e2e_ms, kernel_ms = (float(x) for x in t.cpu())
-        g = torch.tensor([probe_gbps, host_gbps], device=dev, dtype=torch.float64)
-        dist.all_reduce(g, op=dist.ReduceOp.SUM)
-        probe_total, host_total = (float(x) for x in g.cpu())
-    else:
-        probe_total, host_total = probe_gbps, host_gbps
+    pass_ms, e2e_ms, kernel_ms, probe_total, host_total = reduce_over_ranks(pass_ms, e2e_ms, kernel_ms, probe_gbps, host_gbps,
+                                                                             world, dev)
 
     if rank != 0:
         if world > 1:

@@ -481,15 +481,15 @@ Labels probe_labels(const gfdcfg::Config &config) {
     Labels out;
     if (!config.probe_hbm && !config.probe_nvlink) return out;
     int n = 0;
-    int rc = gfd_cuda_device_count(&n);
+    int rc = probe_device_count(&n);
     if (rc) fail("probe requested but no CUDA device is usable (the probes have no CPU fallback)", rc);
     if (config.probe_hbm) {
         double rmin = 1e30, cmin = 1e30;
         for (int d = 0; d < n; d++) {
             gfd_probe_result r;
-            if ((rc = gfd_probe_hbm(d, (size_t)config.probe_bytes, 3, 20, GFD_PROBE_READ, &r))) fail("HBM read probe failed on GPU " + std::to_string(d), rc);
+            if ((rc = probe_hbm(d, (size_t)config.probe_bytes, 3, 20, GFD_PROBE_READ, &r))) fail("HBM read probe failed on GPU " + std::to_string(d), rc);
             rmin = std::min(rmin, r.gbps);
-            if ((rc = gfd_probe_hbm(d, (size_t)config.probe_bytes / 2, 3, 20, GFD_PROBE_COPY, &r))) fail("HBM copy probe failed on GPU " + std::to_string(d), rc);
+            if ((rc = probe_hbm(d, (size_t)config.probe_bytes / 2, 3, 20, GFD_PROBE_COPY, &r))) fail("HBM copy probe failed on GPU " + std::to_string(d), rc);
             cmin = std::min(cmin, r.gbps);
         }
         out["nvidia.com/gpu.probe.hbm.read-gbps"] = std::to_string((long long)rmin);
@@ -504,7 +504,7 @@ Labels probe_labels(const gfdcfg::Config &config) {
             for (int d = 0; d < n; d++) {
                 if (s == d) continue;
                 gfd_probe_result r;
-                rc = gfd_probe_p2p(s, d, bytes, 2, 10, GFD_PROBE_READ, &r);
+                rc = probe_p2p(s, d, bytes, 2, 10, GFD_PROBE_READ, &r);
                 if (rc == GFD_ERR_PEER_ACCESS) continue;
                 if (rc) fail("NVLink probe failed for GPU pair " + std::to_string(s) + "->" + std::to_string(d), rc);
                 pmin = std::min(pmin, r.gbps);

@@ -52,6 +52,10 @@ std::unique_ptr<Manager> new_manager(const gfdcfg::Config &config);
 Labels nvml_labels(Manager &mgr, const gfdcfg::Config &config, bool leave_attached = false);
 // lm.NewVGPULabeler(...).Labels()
 Labels vgpu_labels(const gfdcfg::Config &config);
+// Probe entry points of libgfd_b200.so, bound lazily (probe_loader.cpp); throw PassError if the library is missing.
+int probe_device_count(int *n);
+int probe_hbm(int dev, size_t bytes, int warmup, int iters, int mode, gfd_probe_result *out);
+int probe_p2p(int src, int dst, size_t bytes, int warmup, int iters, int mode, gfd_probe_result *out);
 // NEW opt-in probe labels (empty unless --probe-hbm / --probe-nvlink)
 Labels probe_labels(const gfdcfg::Config &config);
 

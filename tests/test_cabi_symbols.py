@@ -28,10 +28,28 @@ def test_no_link_time_dependency_on_nvml_or_libcuda():
     assert "libnvidia-ml" not in needed and "libcuda.so" not in needed and "libcudart" not in needed
 
 
-def test_binary_is_linked_against_the_shim_not_the_oracle():
+def test_binary_has_no_link_to_the_oracle_or_the_driver_libs():
+    """The labeler carries the host-only C-ABI sources statically and dlopen()s libgfd_b200.so only for the probes."""
     B = importlib.import_module("gpu-feature-discovery_b200.binding")
     needed = subprocess.run(["readelf", "-d", B.BIN_PATH], capture_output=True, text=True, check=True).stdout
-    assert "libgfd_b200.so" in needed and "oracle" not in needed
+    for lib in ("oracle", "libnvidia-ml", "libcuda", "libcudart", "libstdc++"):
+        assert lib not in needed
+    strings = subprocess.run(["strings", "-a", B.BIN_PATH], capture_output=True, text=True, check=True).stdout
+    assert "libgfd_b200.so" in strings and "ref_replay" not in strings and "gfd_oracle" not in strings
+
+
+def test_probe_flag_without_a_gpu_fails_the_pass_loudly(tmp_path):
+    """No CPU fallback: --probe-hbm on a host without a usable CUDA device is an error, not a silent skip."""
+    import torch
+    if torch.cuda.is_available():
+        import pytest
+        pytest.skip("GPU present")
+    B = importlib.import_module("gpu-feature-discovery_b200.binding")
+    out = os.path.join(str(tmp_path), "gfd")
+    p = subprocess.run([B.BIN_PATH, "--oneshot", "--fail-on-init-error=false", "--probe-hbm", "-o", out], capture_output=True, text=True,
+                       env={"PATH": os.environ.get("PATH", "")})
+    assert p.returncode == 1 and not os.path.exists(out)
+    assert "probe requested but no CUDA device is usable" in p.stderr
 
 
 def test_gpu_entry_points_fail_loudly_without_a_gpu():
