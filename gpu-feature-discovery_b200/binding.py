@@ -39,7 +39,7 @@ SYMBOLS = [
     "gfd_dev_is_mig_capable", "gfd_dev_is_mig_enabled", "gfd_dev_mig_count", "gfd_dev_mig_get", "gfd_dev_parent",
     "gfd_dev_attributes", "gfd_dev_uuid", "gfd_mig_memory_size_gb", "gfd_mig_profile_string", "gfd_vgpu_parse",
     "gfd_hbm_fill_pattern", "gfd_hbm_scratch_bytes", "gfd_hbm_read_checksum", "gfd_hbm_read_checksum_noalloc", "gfd_hbm_copy", "gfd_checksum_host",
-    "gfd_probe_hbm", "gfd_probe_p2p", "gfd_cuda_device_by_uuid", "gfd_cuda_device_count",
+    "gfd_probe_hbm", "gfd_probe_p2p", "gfd_probe_p2p_matrix", "gfd_cuda_device_by_uuid", "gfd_cuda_device_count",
 ]
 
 
@@ -110,6 +110,7 @@ _SIG = {
     "gfd_checksum_host": (_int, [_int, _vp, _sz, _P(Checksum)]),
     "gfd_probe_hbm": (_int, [_int, _sz, _int, _int, _int, _P(ProbeResult)]),
     "gfd_probe_p2p": (_int, [_int, _int, _sz, _int, _int, _int, _P(ProbeResult)]),
+    "gfd_probe_p2p_matrix": (_int, [_int, _sz, _int, _int, _int, _P(ctypes.c_double), _P(ctypes.c_double)]),
     "gfd_cuda_device_by_uuid": (_int, [ctypes.c_char_p, _P(_int)]),
     "gfd_cuda_device_count": (_int, [_P(_int)]),
 }
@@ -296,6 +297,13 @@ def probe_p2p(src, dst, nbytes, warmup=3, iters=20, mode=PROBE_READ):
     r = ProbeResult()
     _check(lib.gfd_probe_p2p(src, dst, nbytes, warmup, iters, mode, ctypes.byref(r)), "gfd_probe_p2p")
     return r
+
+
+def probe_p2p_matrix(n, nbytes, warmup=2, iters=10, mode=PROBE_READ):
+    m = (ctypes.c_double * (n * n))()
+    ring = ctypes.c_double()
+    _check(lib.gfd_probe_p2p_matrix(n, nbytes, warmup, iters, mode, m, ctypes.byref(ring)), "gfd_probe_p2p_matrix")
+    return [[m[r * n + c] for c in range(n)] for r in range(n)], ring.value
 
 
 def cuda_device_count():

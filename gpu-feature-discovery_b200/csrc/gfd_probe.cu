@@ -24,6 +24,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <mutex>
+#include <vector>
 
 #include "gfd_internal.h"
 
@@ -567,6 +568,152 @@ GFD_API int gfd_probe_p2p(int src_device, int dst_device, size_t bytes, int warm
         DeviceScope s(dst_device);
         if (dst.p) { cudaFree(dst.p); dst.p = nullptr; }
     }
+    return rc;
+}
+
+// ---- all pairs at once: the round-robin tournament of SURVEY.md 8(e) ---------------------------------------
+// n GPUs (n even): n-1 rounds of n/2 disjoint pairs (circle method); in every round each pair runs BOTH directions
+// at the same time, so all n GPUs pull from a distinct peer concurrently -- 2 * (n/2) = n kernels in flight, each
+// timed with its own events on its own stream.  Then one "shift" round per k = 1..n-1 is NOT needed: the tournament
+// already covers every directed pair exactly once.  Finally an all-at-once ring round (d pulls from d+1) is repeated
+// to report the aggregate.  No NCCL, no collective: nothing is reduced.
+namespace {
+struct P2PDev {
+    void *src = nullptr, *dst = nullptr, *scratch = nullptr, *out = nullptr;
+    cudaStream_t st = nullptr;
+    cudaEvent_t e0 = nullptr, e1 = nullptr;
+};
+
+int p2p_launch(int run_dev, P2PDev &me, const void *peer_src, size_t bytes, int mode, int reps, bool timed) {
+    DeviceScope s(run_dev);
+    if (s.rc) return s.rc;
+    int rc;
+    if (timed) CUDA_TRY(cudaEventRecord(me.e0, me.st));
+    for (int i = 0; i < reps; i++) {
+        if (mode == GFD_PROBE_COPY) rc = launch_copy(run_dev, me.dst, peer_src, bytes, me.st, nullptr);
+        else rc = launch_read(run_dev, peer_src, bytes, static_cast<gfd_checksum *>(me.out), me.scratch, me.st, nullptr);
+        if (rc) return rc;
+    }
+    if (timed) CUDA_TRY(cudaEventRecord(me.e1, me.st));
+    return 0;
+}
+
+int p2p_elapsed(int dev, P2PDev &me, float *ms) {
+    DeviceScope s(dev);
+    if (s.rc) return s.rc;
+    CUDA_TRY(cudaEventSynchronize(me.e1));
+    CUDA_TRY(cudaEventElapsedTime(ms, me.e0, me.e1));
+    return 0;
+}
+}  // namespace
+
+GFD_API int gfd_probe_p2p_matrix(int n_devices, size_t bytes, int warmup, int iters, int mode, double *gbps_matrix,
+                                 double *ring_aggregate_gbps) {
+    int n;
+    int rc = device_count_checked(&n);
+    if (rc) return rc;
+    if (!gbps_matrix || n_devices < 2 || n_devices > n || n_devices > kMaxDevices || bytes == 0 || iters <= 0 || warmup < 0 ||
+        (mode != GFD_PROBE_READ && mode != GFD_PROBE_COPY))
+        return GFD_ERR_BAD_ARGUMENT;
+    const int N = n_devices;
+    for (int i = 0; i < N * N; i++) gbps_matrix[i] = 0.0;
+    std::vector<P2PDev> dev((size_t)N);
+    auto cleanup = [&]() {
+        for (int d = 0; d < N; d++) {
+            DeviceScope s(d);
+            if (dev[d].st) cudaStreamSynchronize(dev[d].st);
+            if (dev[d].src) cudaFree(dev[d].src);
+            if (dev[d].dst) cudaFree(dev[d].dst);
+            if (dev[d].scratch) cudaFree(dev[d].scratch);
+            if (dev[d].out) cudaFree(dev[d].out);
+            if (dev[d].e0) cudaEventDestroy(dev[d].e0);
+            if (dev[d].e1) cudaEventDestroy(dev[d].e1);
+            if (dev[d].st) cudaStreamDestroy(dev[d].st);
+        }
+    };
+    auto body = [&]() -> int {
+        for (int d = 0; d < N; d++) {
+            DeviceScope s(d);
+            if (s.rc) return s.rc;
+            for (int p = 0; p < N; p++) {
+                if (p == d) continue;
+                int can = 0;
+                CUDA_TRY(cudaDeviceCanAccessPeer(&can, d, p));
+                if (!can) return GFD_ERR_PEER_ACCESS;
+                cudaError_t e = cudaDeviceEnablePeerAccess(p, 0);
+                if (e == cudaErrorPeerAccessAlreadyEnabled) (void)cudaGetLastError();
+                else if (e != cudaSuccess) return GFD_ERR_CUDA + (int)e;
+            }
+            CUDA_TRY(cudaMalloc(&dev[d].src, bytes));
+            if (mode == GFD_PROBE_COPY) CUDA_TRY(cudaMalloc(&dev[d].dst, bytes));
+            CUDA_TRY(cudaMalloc(&dev[d].scratch, gfd_hbm_scratch_bytes()));
+            CUDA_TRY(cudaMalloc(&dev[d].out, sizeof(gfd_checksum)));
+            CUDA_TRY(cudaStreamCreateWithFlags(&dev[d].st, cudaStreamNonBlocking));
+            CUDA_TRY(cudaEventCreate(&dev[d].e0));
+            CUDA_TRY(cudaEventCreate(&dev[d].e1));
+            int frc = launch_fill(d, dev[d].src, bytes, (uint64_t)d << 40, dev[d].st);
+            if (frc) return frc;
+            CUDA_TRY(cudaStreamSynchronize(dev[d].st));
+        }
+        // circle method; an odd N gets a bye (partner == N)
+        const int M = (N % 2 == 0) ? N : N + 1;
+        std::vector<int> partner((size_t)M);
+        for (int round = 0; round < M - 1; round++) {
+            for (int i = 0; i < M; i++) partner[(size_t)i] = -1;
+            auto seat = [&](int k) { return k == 0 ? M - 1 : (round + k - 1) % (M - 1); };  // fixed seat + rotating ring
+            for (int k = 0; k < M / 2; k++) {
+                int a = seat(k), b = seat(M - 1 - k);
+                partner[(size_t)a] = b;
+                partner[(size_t)b] = a;
+            }
+            for (int pass = 0; pass < 2; pass++) {  // pass 0 = warm-up launches, pass 1 = timed
+                int reps = pass == 0 ? warmup : iters;
+                if (reps == 0) continue;
+                for (int d = 0; d < N; d++) {
+                    int p = partner[(size_t)d];
+                    if (p < 0 || p >= N) continue;
+                    int lrc = p2p_launch(d, dev[d], dev[p].src, bytes, mode, reps, pass == 1);
+                    if (lrc) return lrc;
+                }
+                for (int d = 0; d < N; d++) {
+                    int p = partner[(size_t)d];
+                    if (p < 0 || p >= N) continue;
+                    DeviceScope s(d);
+                    CUDA_TRY(cudaStreamSynchronize(dev[d].st));
+                    if (pass == 1) {
+                        float ms = 0;
+                        int erc = p2p_elapsed(d, dev[d], &ms);
+                        if (erc) return erc;
+                        gbps_matrix[d * N + p] = (double)bytes * iters / ((double)ms * 1e-3) / 1e9;  // row = puller, column = source
+                    }
+                }
+            }
+        }
+        if (ring_aggregate_gbps) {  // every GPU pulls from its right-hand neighbour at once
+            *ring_aggregate_gbps = 0.0;
+            for (int pass = 0; pass < 2; pass++) {
+                int reps = pass == 0 ? warmup : iters;
+                if (reps == 0) continue;
+                for (int d = 0; d < N; d++) {
+                    int lrc = p2p_launch(d, dev[d], dev[(d + 1) % N].src, bytes, mode, reps, pass == 1);
+                    if (lrc) return lrc;
+                }
+                for (int d = 0; d < N; d++) {
+                    DeviceScope s(d);
+                    CUDA_TRY(cudaStreamSynchronize(dev[d].st));
+                    if (pass == 1) {
+                        float ms = 0;
+                        int erc = p2p_elapsed(d, dev[d], &ms);
+                        if (erc) return erc;
+                        *ring_aggregate_gbps += (double)bytes * iters / ((double)ms * 1e-3) / 1e9;
+                    }
+                }
+            }
+        }
+        return 0;
+    };
+    rc = body();
+    cleanup();
     return rc;
 }
 

@@ -497,21 +497,24 @@ Labels probe_labels(const gfdcfg::Config &config) {
         out["nvidia.com/gpu.probe.hbm.size-mib"] = std::to_string((long long)(config.probe_bytes >> 20));
     }
     if (config.probe_nvlink && n >= 2) {
-        double pmin = 1e30;
-        int pairs = 0;
+        // all directed pairs, concurrently: n-1 rounds of n/2 disjoint pairs, both directions at once
         size_t bytes = (size_t)std::min<int64_t>(config.probe_bytes, 1ll << 30);
-        for (int s = 0; s < n; s++)
-            for (int d = 0; d < n; d++) {
-                if (s == d) continue;
-                gfd_probe_result r;
-                rc = probe_p2p(s, d, bytes, 2, 10, GFD_PROBE_READ, &r);
-                if (rc == GFD_ERR_PEER_ACCESS) continue;
-                if (rc) fail("NVLink probe failed for GPU pair " + std::to_string(s) + "->" + std::to_string(d), rc);
-                pmin = std::min(pmin, r.gbps);
-                pairs++;
-            }
-        out["nvidia.com/gpu.probe.nvlink.pairs"] = std::to_string(pairs);
-        if (pairs) out["nvidia.com/gpu.probe.nvlink.p2p-read-gbps"] = std::to_string((long long)pmin);
+        std::vector<double> m((size_t)n * n, 0.0);
+        double ring = 0.0;
+        rc = probe_p2p_matrix(n, bytes, 2, 10, GFD_PROBE_READ, m.data(), &ring);
+        if (rc == GFD_ERR_PEER_ACCESS) {
+            out["nvidia.com/gpu.probe.nvlink.pairs"] = "0";
+        } else {
+            if (rc) fail("NVLink probe failed", rc);
+            double pmin = 1e30;
+            int pairs = 0;
+            for (int a = 0; a < n; a++)
+                for (int b = 0; b < n; b++)
+                    if (a != b && m[(size_t)a * n + b] > 0) { pmin = std::min(pmin, m[(size_t)a * n + b]); pairs++; }
+            out["nvidia.com/gpu.probe.nvlink.pairs"] = std::to_string(pairs);
+            if (pairs) out["nvidia.com/gpu.probe.nvlink.p2p-read-gbps"] = std::to_string((long long)pmin);
+            out["nvidia.com/gpu.probe.nvlink.ring-gbps"] = std::to_string((long long)ring);
+        }
     }
     return out;
 }

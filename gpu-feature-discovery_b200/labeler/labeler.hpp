@@ -56,6 +56,7 @@ Labels vgpu_labels(const gfdcfg::Config &config);
 int probe_device_count(int *n);
 int probe_hbm(int dev, size_t bytes, int warmup, int iters, int mode, gfd_probe_result *out);
 int probe_p2p(int src, int dst, size_t bytes, int warmup, int iters, int mode, gfd_probe_result *out);
+int probe_p2p_matrix(int n, size_t bytes, int warmup, int iters, int mode, double *matrix, double *ring);
 // NEW opt-in probe labels (empty unless --probe-hbm / --probe-nvlink)
 Labels probe_labels(const gfdcfg::Config &config);
 

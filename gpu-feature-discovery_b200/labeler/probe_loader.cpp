@@ -20,6 +20,7 @@ struct ProbeApi {
     int (*device_count)(int *) = nullptr;
     int (*probe_hbm)(int, size_t, int, int, int, gfd_probe_result *) = nullptr;
     int (*probe_p2p)(int, int, size_t, int, int, int, gfd_probe_result *) = nullptr;
+    int (*probe_p2p_matrix)(int, size_t, int, int, int, double *, double *) = nullptr;
     bool loaded = false;
 };
 ProbeApi g_api;
@@ -42,7 +43,8 @@ void load() {
     *(void **)&g_api.device_count = dlsym(lib, "gfd_cuda_device_count");
     *(void **)&g_api.probe_hbm = dlsym(lib, "gfd_probe_hbm");
     *(void **)&g_api.probe_p2p = dlsym(lib, "gfd_probe_p2p");
-    if (!g_api.device_count || !g_api.probe_hbm || !g_api.probe_p2p)
+    *(void **)&g_api.probe_p2p_matrix = dlsym(lib, "gfd_probe_p2p_matrix");
+    if (!g_api.device_count || !g_api.probe_hbm || !g_api.probe_p2p || !g_api.probe_p2p_matrix)
         throw PassError("probe requested but " + path + " does not export the probe entry points of include/gfd_b200.h");
     g_api.loaded = true;
 }
@@ -56,6 +58,11 @@ int probe_hbm(int dev, size_t bytes, int warmup, int iters, int mode, gfd_probe_
 int probe_p2p(int src, int dst, size_t bytes, int warmup, int iters, int mode, gfd_probe_result *out) {
     load();
     return g_api.probe_p2p(src, dst, bytes, warmup, iters, mode, out);
+}
+
+int probe_p2p_matrix(int n, size_t bytes, int warmup, int iters, int mode, double *matrix, double *ring) {
+    load();
+    return g_api.probe_p2p_matrix(n, bytes, warmup, iters, mode, matrix, ring);
 }
 
 }  // namespace gfdlm

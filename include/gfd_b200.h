@@ -253,6 +253,12 @@ int gfd_probe_hbm(int cuda_device, size_t bytes, int warmup, int iters, int mode
  * through a peer mapping (read = fold, copy = store locally).  No NCCL: nothing is reduced. */
 int gfd_probe_p2p(int src_device, int dst_device, size_t bytes, int warmup, int iters, int mode,
                   gfd_probe_result *out);
+/* All directed pairs of the first n_devices GPUs, measured CONCURRENTLY: n-1 rounds of n/2 disjoint pairs (round-robin
+ * tournament), both directions of every pair at once, so each round keeps all n GPUs pulling from a distinct peer.
+ * gbps_matrix[puller * n + source] receives GB/s (diagonal 0).  *ring_aggregate_gbps (optional) = sum over GPUs when
+ * every GPU pulls from its right-hand neighbour simultaneously.  One kernel per direction, no NCCL, no collective. */
+int gfd_probe_p2p_matrix(int n_devices, size_t bytes, int warmup, int iters, int mode, double *gbps_matrix,
+                         double *ring_aggregate_gbps);
 /* CUDA ordinal whose UUID equals `uuid` ("GPU-xxxxxxxx-...."), or an error. */
 int gfd_cuda_device_by_uuid(const char *uuid, int *ordinal);
 int gfd_cuda_device_count(int *count);

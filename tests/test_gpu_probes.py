@@ -197,3 +197,19 @@ def test_p2p_probe(env):
     assert 50 < r.gbps < 2000, r.gbps
     c = B.probe_p2p(1, 0, n, warmup=2, iters=5, mode=B.PROBE_COPY)
     assert 50 < c.gbps < 2000, c.gbps
+
+
+def test_p2p_matrix_concurrent_tournament(env):
+    """gfd_probe_p2p_matrix: every directed pair measured, all GPUs busy in every round; needs >= 2 GPUs."""
+    B = env.B
+    n = env.torch.cuda.device_count()
+    if n < 2:
+        pytest.skip("needs 2 GPUs")
+    m, ring = B.probe_p2p_matrix(n, 1 << 28, warmup=1, iters=5, mode=B.PROBE_READ)
+    for a in range(n):
+        for b in range(n):
+            if a == b:
+                assert m[a][b] == 0.0
+            else:
+                assert 50 < m[a][b] < 2000, (a, b, m[a][b])
+    assert ring > 50 * n
