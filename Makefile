@@ -77,3 +77,10 @@ asan:
 	    -shared -cudart static -x cu $(LIB_SRCS) -o $(ASAN_DIR)/libgfd_b200.so -ldl -lpthread -lasan -lubsan
 	/usr/bin/g++ $(CXXFLAGS) $(ASAN_FLAGS) -fPIE -I$(CSRC) -I$(CUDA_INC) $(LABELER_SRCS) $(CORE_SRCS) -o $(ASAN_DIR)/gpu-feature-discovery -ldl -lpthread
 .PHONY: asan
+
+# ThreadSanitizer build of the labeler (the per-GPU attach/query threads): `make tsan`, then
+#      GFD_TEST_BINDIR=build/tsan python -m pytest tests/test_cli_parity.py
+tsan:
+	@mkdir -p build/tsan
+	/usr/bin/g++ -O1 -g -std=c++17 -fsanitize=thread -fPIE -Iinclude -I$(CSRC) -I$(CUDA_INC) $(LABELER_SRCS) $(CORE_SRCS) -o build/tsan/gpu-feature-discovery -ldl -lpthread
+.PHONY: tsan
