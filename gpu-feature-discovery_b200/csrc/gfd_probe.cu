@@ -485,7 +485,7 @@ int time_kernel(int run_dev, void *dst, const void *src, size_t bytes, int warmu
     CUDA_TRY(cudaEventCreate(&e1.e));
     int grid = 0;
     auto once = [&]() -> int {
-        if (mode == GFD_PROBE_COPY) return launch_copy(run_dev, dst, src, bytes, st.s, &grid);
+        if (mode == GFD_PROBE_COPY || mode == GFD_PROBE_PUSH) return launch_copy(run_dev, dst, src, bytes, st.s, &grid);
         return launch_read(run_dev, src, bytes, static_cast<gfd_checksum *>(d_out.p), scratch.p, st.s, &grid);
     };
     for (int i = 0; i < warmup; i++)
@@ -538,10 +538,14 @@ GFD_API int gfd_probe_p2p(int src_device, int dst_device, size_t bytes, int warm
     int rc = device_count_checked(&n);
     if (rc) return rc;
     if (!out || src_device < 0 || dst_device < 0 || src_device >= n || dst_device >= n || src_device == dst_device ||
-        bytes == 0 || iters <= 0 || warmup < 0 || (mode != GFD_PROBE_READ && mode != GFD_PROBE_COPY))
+        bytes == 0 || iters <= 0 || warmup < 0 || (mode != GFD_PROBE_READ && mode != GFD_PROBE_COPY && mode != GFD_PROBE_PUSH))
         return GFD_ERR_BAD_ARGUMENT;
+    // pull modes run on the destination GPU and load from the source's memory; push runs on the source GPU and stores
+    // into the destination's memory (posted writes: no request/response round trip on the link)
+    const int run_device = (mode == GFD_PROBE_PUSH) ? src_device : dst_device;
+    const int far_device = (mode == GFD_PROBE_PUSH) ? dst_device : src_device;
     int can = 0;
-    CUDA_TRY(cudaDeviceCanAccessPeer(&can, dst_device, src_device));
+    CUDA_TRY(cudaDeviceCanAccessPeer(&can, run_device, far_device));
     if (!can) return GFD_ERR_PEER_ACCESS;
     Buf src, dst;
     {
@@ -552,14 +556,18 @@ GFD_API int gfd_probe_p2p(int src_device, int dst_device, size_t bytes, int warm
         CUDA_TRY(cudaDeviceSynchronize());
     }
     {
-        DeviceScope s(dst_device);
+        DeviceScope s(run_device);
         if (s.rc) return s.rc;
-        cudaError_t e = cudaDeviceEnablePeerAccess(src_device, 0);
+        cudaError_t e = cudaDeviceEnablePeerAccess(far_device, 0);
         if (e == cudaErrorPeerAccessAlreadyEnabled) (void)cudaGetLastError();
         else if (e != cudaSuccess) return GFD_ERR_CUDA + (int)e;
-        if (mode == GFD_PROBE_COPY) CUDA_TRY(cudaMalloc(&dst.p, bytes));
     }
-    rc = time_kernel(dst_device, dst.p, src.p, bytes, warmup, iters, mode, out);
+    if (mode != GFD_PROBE_READ) {
+        DeviceScope s(dst_device);
+        if (s.rc) return s.rc;
+        CUDA_TRY(cudaMalloc(&dst.p, bytes));
+    }
+    rc = time_kernel(run_device, dst.p, src.p, bytes, warmup, iters, mode, out);
     {
         DeviceScope s(src_device);  // free on the owning device
         if (src.p) { cudaFree(src.p); src.p = nullptr; }
@@ -591,6 +599,7 @@ int p2p_launch(int run_dev, P2PDev &me, const void *peer_src, size_t bytes, int 
     if (timed) CUDA_TRY(cudaEventRecord(me.e0, me.st));
     for (int i = 0; i < reps; i++) {
         if (mode == GFD_PROBE_COPY) rc = launch_copy(run_dev, me.dst, peer_src, bytes, me.st, nullptr);
+        else if (mode == GFD_PROBE_PUSH) rc = launch_copy(run_dev, const_cast<void *>(peer_src), me.src, bytes, me.st, nullptr);  // peer_src = the partner's dst
         else rc = launch_read(run_dev, peer_src, bytes, static_cast<gfd_checksum *>(me.out), me.scratch, me.st, nullptr);
         if (rc) return rc;
     }
@@ -613,7 +622,7 @@ GFD_API int gfd_probe_p2p_matrix(int n_devices, size_t bytes, int warmup, int it
     int rc = device_count_checked(&n);
     if (rc) return rc;
     if (!gbps_matrix || n_devices < 2 || n_devices > n || n_devices > kMaxDevices || bytes == 0 || iters <= 0 || warmup < 0 ||
-        (mode != GFD_PROBE_READ && mode != GFD_PROBE_COPY))
+        (mode != GFD_PROBE_READ && mode != GFD_PROBE_COPY && mode != GFD_PROBE_PUSH))
         return GFD_ERR_BAD_ARGUMENT;
     const int N = n_devices;
     for (int i = 0; i < N * N; i++) gbps_matrix[i] = 0.0;
@@ -645,7 +654,7 @@ GFD_API int gfd_probe_p2p_matrix(int n_devices, size_t bytes, int warmup, int it
                 else if (e != cudaSuccess) return GFD_ERR_CUDA + (int)e;
             }
             CUDA_TRY(cudaMalloc(&dev[d].src, bytes));
-            if (mode == GFD_PROBE_COPY) CUDA_TRY(cudaMalloc(&dev[d].dst, bytes));
+            if (mode != GFD_PROBE_READ) CUDA_TRY(cudaMalloc(&dev[d].dst, bytes));
             CUDA_TRY(cudaMalloc(&dev[d].scratch, gfd_hbm_scratch_bytes()));
             CUDA_TRY(cudaMalloc(&dev[d].out, sizeof(gfd_checksum)));
             CUDA_TRY(cudaStreamCreateWithFlags(&dev[d].st, cudaStreamNonBlocking));
@@ -672,7 +681,7 @@ GFD_API int gfd_probe_p2p_matrix(int n_devices, size_t bytes, int warmup, int it
                 for (int d = 0; d < N; d++) {
                     int p = partner[(size_t)d];
                     if (p < 0 || p >= N) continue;
-                    int lrc = p2p_launch(d, dev[d], dev[p].src, bytes, mode, reps, pass == 1);
+                    int lrc = p2p_launch(d, dev[d], mode == GFD_PROBE_PUSH ? dev[p].dst : dev[p].src, bytes, mode, reps, pass == 1);
                     if (lrc) return lrc;
                 }
                 for (int d = 0; d < N; d++) {
@@ -695,7 +704,7 @@ GFD_API int gfd_probe_p2p_matrix(int n_devices, size_t bytes, int warmup, int it
                 int reps = pass == 0 ? warmup : iters;
                 if (reps == 0) continue;
                 for (int d = 0; d < N; d++) {
-                    int lrc = p2p_launch(d, dev[d], dev[(d + 1) % N].src, bytes, mode, reps, pass == 1);
+                    int lrc = p2p_launch(d, dev[d], mode == GFD_PROBE_PUSH ? dev[(d + 1) % N].dst : dev[(d + 1) % N].src, bytes, mode, reps, pass == 1);
                     if (lrc) return lrc;
                 }
                 for (int d = 0; d < N; d++) {

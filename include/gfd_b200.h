@@ -237,7 +237,7 @@ int gfd_hbm_read_checksum_noalloc(const void *d_buf, size_t bytes, gfd_checksum 
 int gfd_checksum_host(int cuda_device, const void *host_buf, size_t bytes, gfd_checksum *out);
 
 /* Self-contained probes: allocate, fill, warm up, time `iters` launches with CUDA events, free. */
-enum gfd_probe_mode { GFD_PROBE_READ = 0, GFD_PROBE_COPY = 1 };
+enum gfd_probe_mode { GFD_PROBE_READ = 0, GFD_PROBE_COPY = 1, GFD_PROBE_PUSH = 2 /* p2p only: the source GPU stores into the peer */ };
 typedef struct gfd_probe_result {
     double gbps;           /* algorithmic bytes (bytes, or 2*bytes for copy over HBM; bytes per direction for p2p) / time */
     double ms_per_launch;
@@ -255,7 +255,8 @@ int gfd_probe_p2p(int src_device, int dst_device, size_t bytes, int warmup, int 
                   gfd_probe_result *out);
 /* All directed pairs of the first n_devices GPUs, measured CONCURRENTLY: n-1 rounds of n/2 disjoint pairs (round-robin
  * tournament), both directions of every pair at once, so each round keeps all n GPUs pulling from a distinct peer.
- * gbps_matrix[puller * n + source] receives GB/s (diagonal 0).  *ring_aggregate_gbps (optional) = sum over GPUs when
+ * gbps_matrix[runner * n + peer] receives GB/s (diagonal 0); runner = the GPU whose kernel moved the bytes (the puller for
+ * READ/COPY, the pusher for PUSH).  *ring_aggregate_gbps (optional) = sum over GPUs when
  * every GPU pulls from its right-hand neighbour simultaneously.  One kernel per direction, no NCCL, no collective. */
 int gfd_probe_p2p_matrix(int n_devices, size_t bytes, int warmup, int iters, int mode, double *gbps_matrix,
                          double *ring_aggregate_gbps);
