@@ -484,17 +484,28 @@ Labels probe_labels(const gfdcfg::Config &config) {
     int rc = probe_device_count(&n);
     if (rc) fail("probe requested but no CUDA device is usable (the probes have no CPU fallback)", rc);
     if (config.probe_hbm) {
+        // A probe is a guest on the GPU: when the requested buffer does not fit beside what already lives in HBM (a MIG
+        // slice, a running job) it halves the size down to 256 MiB -- still >> the 126 MB L2 -- before giving up.
+        const int kOutOfMemory = GFD_ERR_CUDA + 2;  // cudaErrorMemoryAllocation
+        auto run = [&](int d, size_t bytes, int mode, gfd_probe_result *r, size_t *used) {
+            int e;
+            while ((e = probe_hbm(d, bytes, 3, 20, mode, r)) == kOutOfMemory && bytes > ((size_t)256 << 20)) bytes /= 2;
+            *used = bytes;
+            return e;
+        };
         double rmin = 1e30, cmin = 1e30;
+        size_t size_min = (size_t)config.probe_bytes, used = 0;
         for (int d = 0; d < n; d++) {
             gfd_probe_result r;
-            if ((rc = probe_hbm(d, (size_t)config.probe_bytes, 3, 20, GFD_PROBE_READ, &r))) fail("HBM read probe failed on GPU " + std::to_string(d), rc);
+            if ((rc = run(d, (size_t)config.probe_bytes, GFD_PROBE_READ, &r, &used))) fail("HBM read probe failed on GPU " + std::to_string(d), rc);
             rmin = std::min(rmin, r.gbps);
-            if ((rc = probe_hbm(d, (size_t)config.probe_bytes / 2, 3, 20, GFD_PROBE_COPY, &r))) fail("HBM copy probe failed on GPU " + std::to_string(d), rc);
+            size_min = std::min(size_min, used);
+            if ((rc = run(d, (size_t)config.probe_bytes / 2, GFD_PROBE_COPY, &r, &used))) fail("HBM copy probe failed on GPU " + std::to_string(d), rc);
             cmin = std::min(cmin, r.gbps);
         }
         out["nvidia.com/gpu.probe.hbm.read-gbps"] = std::to_string((long long)rmin);
         out["nvidia.com/gpu.probe.hbm.copy-gbps"] = std::to_string((long long)cmin);
-        out["nvidia.com/gpu.probe.hbm.size-mib"] = std::to_string((long long)(config.probe_bytes >> 20));
+        out["nvidia.com/gpu.probe.hbm.size-mib"] = std::to_string((long long)(size_min >> 20));
     }
     if (config.probe_nvlink && n >= 2) {
         // all directed pairs, concurrently: n-1 rounds of n/2 disjoint pairs, both directions at once
