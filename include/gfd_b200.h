@@ -207,7 +207,9 @@ typedef struct gfd_checksum {
 
 /* Fill `bytes` at d_buf with word[i] = 0x9E3779B97F4A7C15 * (i + seed) (SURVEY.md 8(d) probe input). */
 int gfd_hbm_fill_pattern(void *d_buf, size_t bytes, uint64_t seed, void *stream);
-/* Bytes of device scratch gfd_hbm_read_checksum needs (per-block partial sums), for any size. */
+/* Bytes of device scratch gfd_hbm_read_checksum needs, for any input size: a 16-byte header (the tile counter the
+ * CTAs draw work from; the call clears it on `stream` before launching) + one 16-byte partial sum per CTA.  The
+ * scratch needs no initialisation by the caller, but two calls sharing one scratch must not overlap on the GPU. */
 size_t gfd_hbm_scratch_bytes(void);
 /* hbm_read_probe: stream `bytes` from HBM with 128-bit coalesced loads and fold them into *d_out
  * (device memory).  Algorithmic traffic: `bytes` read.  d_scratch: gfd_hbm_scratch_bytes() bytes. */

@@ -213,3 +213,25 @@ def test_p2p_matrix_concurrent_tournament(env):
             else:
                 assert 50 < m[a][b] < 2000, (a, b, m[a][b])
     assert ring > 50 * n
+
+
+def test_random_sizes_and_offsets(env):
+    """40 random (offset, size) windows of one random buffer: read checksum and copy vs the C oracle / numpy, bit-exact."""
+    torch = env.torch
+    rng = np.random.default_rng(20261106)
+    total = (96 << 20) + 4096
+    host = rng.integers(0, 256, size=total, dtype=np.uint8)
+    buf = torch.from_numpy(host).to(env.dev)
+    dst = torch.empty(total + 64, dtype=torch.uint8, device=env.dev)
+    st = torch.cuda.current_stream().cuda_stream
+    for _ in range(40):
+        off = int(rng.integers(0, 4096)) * 16
+        n = int(rng.choice([rng.integers(0, 70000), rng.integers(0, 1 << 20), rng.integers(0, total - off)]))
+        n = min(n, total - off)
+        view = buf[off:off + n] if n else buf[off:off]
+        assert gpu_checksum(env, view, n) == oracle_checksum(env, host[off:off + n]), (off, n)
+        dst.fill_(0x5A)
+        env.B.hbm_copy(dst.data_ptr(), buf.data_ptr() + off, n, st)
+        torch.cuda.synchronize()
+        got = dst.cpu().numpy()
+        assert np.array_equal(got[:n], host[off:off + n]) and (got[n:n + 64] == 0x5A).all(), (off, n)
