@@ -30,6 +30,8 @@ endif
 ifneq ($(LABELER_SRCS),)
 TARGETS += $(BIN)
 endif
+DEMO := examples/cabi_demo
+TARGETS += $(DEMO)
 
 all: $(TARGETS)
 
@@ -60,6 +62,9 @@ $(REPLAY): oracle/ref_replay.c
 CORE_SRCS := $(CSRC)/gfd_nvml.cpp $(CSRC)/gfd_mig_profile.cpp $(CSRC)/gfd_cuda_mgr.cpp
 $(BIN): $(LABELER_SRCS) $(CORE_SRCS) $(CSRC)/gfd_internal.h $(LIB) include/gfd_b200.h $(wildcard $(PKG)/labeler/*.hpp)
 	$(CXX) $(CXXFLAGS) -fPIE -I$(CSRC) -I$(CUDA_INC) $(LABELER_SRCS) $(CORE_SRCS) -o $@ -static-libstdc++ -static-libgcc -Wl,--gc-sections -s -ldl -lpthread
+
+$(DEMO): examples/cabi_demo.c $(LIB) include/gfd_b200.h
+	$(CC) -O2 -Wall -Wextra -Iinclude $< -o $@ -L$(PKG) -lgfd_b200 -Wl,-rpath,'$$ORIGIN/../$(PKG)'
 
 clean:
 	rm -f $(LIB) $(BIN) $(FAKE) $(FAKE_NOMIG) $(FAKE_CUDA) $(ORACLE_SO) $(REPLAY)
