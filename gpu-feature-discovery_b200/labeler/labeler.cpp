@@ -398,22 +398,48 @@ std::unique_ptr<Manager> new_manager(const gfdcfg::Config &config) {
 }
 
 // ---- NewNVMLLabeler (internal/lm/nvml.go:29-72) ----------------------------------------------------
-Labels nvml_labels(Manager &mgr, const gfdcfg::Config &config, bool leave_attached) {
+Labels nvml_labels(Manager &mgr, const gfdcfg::Config &config, bool leave_attached, PhaseTimes *times) {
+    auto now = [] {
+        timespec ts;
+        clock_gettime(CLOCK_MONOTONIC, &ts);
+        return ts.tv_sec * 1e3 + ts.tv_nsec / 1e6;
+    };
+    PhaseTimes local;
+    PhaseTimes &t = times ? *times : local;
+    t = PhaseTimes();
+    double t0 = now();
     try {
         mgr.init();
     } catch (const PassError &e) {
         throw PassError(std::string("error creating NVML labeler: ") + e.what());
     }
+    t.init_ms = now() - t0;
     struct Guard {  // defer manager.Shutdown()
         Manager &m;
         bool skip;
-        ~Guard() { if (!skip) m.shutdown(); }
-    } guard{mgr, leave_attached};
+        PhaseTimes &t;
+        double (*clock)();
+        ~Guard() {
+            if (skip) return;
+            double a = clock();
+            m.shutdown();
+            t.shutdown_ms = clock() - a;
+        }
+    } guard{mgr, leave_attached, t, +now};
     Labels out;
     g_current_tables = config.current_tables;
     try {
+        double t1 = now();
         mgr.prefetch(config.prefetch_threads);  // 0 = one host thread per GPU (no-op on 0/1-GPU nodes), 1 = serial
-        if (mgr.devices().empty()) return out;
+        bool none = mgr.devices().empty();
+        t.attach_ms = now() - t1;
+        if (none) return out;
+        struct Tail {  // everything after the walk: label building from (mostly cached) answers
+            PhaseTimes &t;
+            double start;
+            double (*clock)();
+            ~Tail() { t.labels_ms = clock() - start; }
+        } tail{t, now(), +now};
         machine_type_label(out, *config.machine_type_file);
         version_labels(out, mgr);
         mig_capability_label(out, mgr);

@@ -65,7 +65,8 @@ bool run(gfdlm::Manager &mgr, const gfdcfg::Config &config, const sigset_t &sigs
     while (true) {
         double t0 = now_ms();
         const bool last_pass = *config.oneshot || (config.passes > 0 && passes_done + 1 >= config.passes);
-        gfdlm::Labels nvml = gfdlm::nvml_labels(mgr, config, last_pass);  // lm.NewLabelers: the eager NVML part
+        gfdlm::PhaseTimes ph;
+        gfdlm::Labels nvml = gfdlm::nvml_labels(mgr, config, last_pass, &ph);  // lm.NewLabelers: the eager NVML part
         double t1 = now_ms();
         gfdlm::Labels labels = timestamp;                      // lm.Merge(timestampLabeler, loopLabelers): later wins
         for (auto &kv : nvml) labels[kv.first] = kv.second;
@@ -87,7 +88,9 @@ bool run(gfdlm::Manager &mgr, const gfdcfg::Config &config, const sigset_t &sigs
             throw gfdlm::PassError("error writing file '" + *config.output_file + "': " + e.what());
         }
         double t3 = now_ms();
-        if (config.timing) logf("timing: pass %.3f ms (nvml %.3f, vgpu %.3f, write %.3f)", t3 - t0, t1 - t0, t2 - t1, t3 - t2);
+        if (config.timing)
+            logf("timing: pass %.3f ms (nvml %.3f, vgpu %.3f, write %.3f) [init %.3f, attach %.3f, labels %.3f, shutdown %.3f]", t3 - t0, t1 - t0,
+                 t2 - t1, t3 - t2, ph.init_ms, ph.attach_ms, ph.labels_ms, ph.shutdown_ms);
 
         if (last_pass) { g_fast_exit = true; return false; }
         ++passes_done;
