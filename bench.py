@@ -93,11 +93,22 @@ class ClockSampler(threading.Thread):
         return {"sm_mhz": statistics.median(sm), "sm_max_mhz": max(mx), "reasons": sorted(reasons), "samples": len(sm)}
 
 
+PHASES = {}  # filled by parse_timing: mean ms of the NVML bracket's phases over the steady-state passes of the last run
+
+
 def parse_timing(stderr):
-    out = []
+    out, ph = [], []
     for line in stderr.splitlines():
         if "timing: pass " in line:
             out.append(float(line.split("timing: pass ")[1].split(" ms")[0]))
+            if "[init " in line:
+                body = line.split("[init ")[1].rstrip("]")
+                vals = [float(x.split()[-1]) for x in ("init " + body).split(",")]
+                ph.append(vals)
+    if len(ph) > 1:
+        steady = ph[:-1]
+        PHASES.clear()
+        PHASES.update({k: round(sum(v[i] for v in steady) / len(steady), 3) for i, k in enumerate(("init", "attach", "labels", "shutdown"))})
     return out
 
 
@@ -237,10 +248,11 @@ def main():
     # that runs it -- once, over all N GPUs, with the labeler's own per-GPU host threads -- while the other ranks
     # wait at the barrier.  N copies of a node-level daemon hammering one driver would measure contention, not GFD.
     barrier()
-    pass_ms, product_text = 0.0, ""
+    pass_ms, product_text, phases = 0.0, "", {}
     if rank == 0:
         ms = product_passes(B.BIN_PATH, args.warmup + args.steps, out_file)[args.warmup:]
         pass_ms = sum(ms) / len(ms)
+        phases = dict(PHASES)
         product_text = open(out_file).read()
     barrier()
 
@@ -353,6 +365,7 @@ def main():
         "gpu_launches": launches,
         "label_diff": {"vs_cpu_baseline": diff_lines(product_text, replay_text), "vs_oracle_pynvml": diff_lines(product_text, oracle_text),
                        "labels": len(product_text.splitlines())},
+        "labeling_pass_phases_ms": phases,
         "labeling_pass_ms_keep_attached": round(sum(keep) / len(keep), 4),
         "probe_hbm_read_gbps": round(probe_total, 1),
         "probe_checksum_ok": checksum_ok,
