@@ -20,7 +20,7 @@ What it reads (all paths under the reference root) and what it writes
         known-answer blobs used by vgpu_test.go / pciutil_test.go
         -> vgpu_blobs.json (hex)
   tests/expected-output*.txt         the run()-level regex goldens
-        -> expected-output*.txt (verbatim copies: they are test fixtures)
+        -> expected_output_regexes.json ({file name: [regex lines]})
 
 The Go test tables are parsed with a tiny recursive-descent parser for the
 subset of Go expression syntax those tables use (composite literals, calls,
@@ -30,7 +30,6 @@ reference's tables change, re-running this script changes the fixtures.
 import json
 import os
 import re
-import shutil
 import sys
 
 REF = sys.argv[1] if len(sys.argv) > 1 else "/root/reference"
@@ -374,11 +373,16 @@ def main():
             "blobs": blobs, "expect": expect}, f, indent=1)
         f.write("\n")
 
-    # --- regex goldens (tests/expected-output*.txt), verbatim
+    # --- regex goldens (tests/expected-output*.txt): one JSON holding every file's regex lines
+    goldens = {"cite": "tests/expected-output.txt, -mig-none.txt, -mig-single.txt, -mig-mixed.txt, -vgpu.txt (used by "
+                       "cmd/gpu-feature-discovery/main_test.go:403-435 and tests/integration-tests.py:12-33)", "files": {}}
     for fn in sorted(os.listdir(os.path.join(REF, "tests"))):
         if fn.startswith("expected-output") and fn.endswith(".txt"):
-            shutil.copyfile(os.path.join(REF, "tests", fn), os.path.join(OUT, fn))
-            os.chmod(os.path.join(OUT, fn), 0o644)
+            with open(os.path.join(REF, "tests", fn)) as f:
+                goldens["files"][fn] = f.read().rstrip("\n").split("\n")
+    with open(os.path.join(OUT, "expected_output_regexes.json"), "w") as f:
+        json.dump(goldens, f, indent=1)
+        f.write("\n")
 
     n = sum(len(v["cases"]) for v in vectors.values() if isinstance(v, dict) and "cases" in v)
     print("wrote %d lm cases, %d init-matrix rows, 2 vGPU blobs" % (n, len(matrix)))

@@ -29,7 +29,8 @@ def check_labels(expected_regexs, labels):
 
 
 def expected(name="expected-output.txt"):
-    return [re.compile(l.strip()) for l in open(os.path.join(GOLDEN, name)).readlines()]
+    import json
+    return [re.compile(l.strip()) for l in json.load(open(os.path.join(GOLDEN, "expected_output_regexes.json")))["files"][name]]
 
 
 def run_daemon_and_collect(tmp_path, spawn):

@@ -114,7 +114,7 @@ def test_vgpu_labels_from_mock():
 # ---- run()-level goldens (cmd/gpu-feature-discovery/main_test.go, mig_test.go) ---------------------------
 def check_result(text, expected_file, is_vgpu):
     """checkResult (main_test.go:403-435): every (non-)vgpu line must match >= 1 regex (unanchored)."""
-    regexps = [re.compile(l) for l in open(os.path.join(GOLDEN, expected_file)).read().rstrip("\n").split("\n")]
+    regexps = [re.compile(l) for l in json.load(open(os.path.join(GOLDEN, "expected_output_regexes.json")))["files"][expected_file]]
     for line in text.rstrip("\n").split("\n"):
         if ("vgpu" in line) != is_vgpu:
             continue
