@@ -417,7 +417,7 @@ struct Staging {
     cudaStream_t st = nullptr;
 };
 Staging g_staging[kMaxDevices];
-std::mutex g_staging_mu;
+std::mutex g_staging_mu[kMaxDevices];  // one host-path call at a time PER DEVICE (the staging buffer is shared per device)
 constexpr size_t kHostPathMax = 16ull << 30;  // 16 GiB per call
 }  // namespace
 
@@ -429,7 +429,7 @@ GFD_API int gfd_checksum_host(int cuda_device, const void *host_buf, size_t byte
     if (bytes > kHostPathMax) return GFD_ERR_SIZE_LIMIT;
     DeviceScope scope(cuda_device);
     if (scope.rc) return scope.rc;
-    std::lock_guard<std::mutex> lk(g_staging_mu);  // staging is shared per device: one host-path call at a time
+    std::lock_guard<std::mutex> lk(g_staging_mu[cuda_device]);
     Staging &s = g_staging[cuda_device];
     if (!s.st) {
         CUDA_TRY(cudaStreamCreateWithFlags(&s.st, cudaStreamNonBlocking));
