@@ -64,7 +64,8 @@ bool run(gfdlm::Manager &mgr, const gfdcfg::Config &config, const sigset_t &sigs
     int passes_done = 0;
     while (true) {
         double t0 = now_ms();
-        const bool last_pass = *config.oneshot || (config.passes > 0 && passes_done + 1 >= config.passes);
+        static const bool no_fast_exit = getenv("GFD_B200_NO_FAST_EXIT") != nullptr;  // measurement knob
+        const bool last_pass = !no_fast_exit && (*config.oneshot || (config.passes > 0 && passes_done + 1 >= config.passes));
         gfdlm::PhaseTimes ph;
         gfdlm::Labels nvml = gfdlm::nvml_labels(mgr, config, last_pass, &ph);  // lm.NewLabelers: the eager NVML part
         double t1 = now_ms();
@@ -93,6 +94,8 @@ bool run(gfdlm::Manager &mgr, const gfdcfg::Config &config, const sigset_t &sigs
                  t2 - t1, t3 - t2, ph.init_ms, ph.attach_ms, ph.labels_ms, ph.shutdown_ms);
 
         if (last_pass) { g_fast_exit = true; return false; }
+        if (*config.oneshot) return false;
+        if (config.passes > 0 && passes_done + 1 >= config.passes) return false;
         ++passes_done;
 
         logf("Sleeping for %s", gocompat::duration_string(*config.sleep_interval_ns).c_str());
