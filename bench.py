@@ -105,24 +105,21 @@ def parse_timing(stderr):
                 body = line.split("[init ")[1].rstrip("]")
                 vals = [float(x.split()[-1]) for x in ("init " + body).split(",")]
                 ph.append(vals)
-    if len(ph) > 1:
-        steady = ph[:-1]
+    if ph:
         PHASES.clear()
-        PHASES.update({k: round(sum(v[i] for v in steady) / len(steady), 3) for i, k in enumerate(("init", "attach", "labels", "shutdown"))})
+        PHASES.update({k: round(sum(v[i] for v in ph) / len(ph), 3) for i, k in enumerate(("init", "attach", "labels", "shutdown"))})
     return out
 
 
 def product_passes(binary, passes, out_file, extra=()):
-    # one extra pass is run and dropped: the LAST pass of a process skips nvmlShutdown (fast exit), so it is
-    # not a steady-state pass and must not flatter the mean
-    p = subprocess.run([binary, "--passes", str(passes + 1), "--sleep-interval", "0s", "--timing", "--no-timestamp", "--mig-strategy=none",
+    p = subprocess.run([binary, "--passes", str(passes), "--sleep-interval", "0s", "--timing", "--no-timestamp", "--mig-strategy=none",
                         "-o", out_file] + list(extra), capture_output=True, text=True, timeout=600)
     if p.returncode != 0:
         raise RuntimeError("gpu-feature-discovery failed:\n" + p.stderr[-2000:])
     ms = parse_timing(p.stderr)
-    if len(ms) != passes + 1:
-        raise RuntimeError("expected %d timing lines, got %d" % (passes + 1, len(ms)))
-    return ms[:-1]
+    if len(ms) != passes:
+        raise RuntimeError("expected %d timing lines, got %d" % (passes, len(ms)))
+    return ms
 
 
 def product_oneshot(binary, out_file):

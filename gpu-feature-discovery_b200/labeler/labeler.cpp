@@ -398,7 +398,7 @@ std::unique_ptr<Manager> new_manager(const gfdcfg::Config &config) {
 }
 
 // ---- NewNVMLLabeler (internal/lm/nvml.go:29-72) ----------------------------------------------------
-Labels nvml_labels(Manager &mgr, const gfdcfg::Config &config, bool leave_attached, PhaseTimes *times) {
+Labels nvml_labels(Manager &mgr, const gfdcfg::Config &config, PhaseTimes *times) {
     auto now = [] {
         timespec ts;
         clock_gettime(CLOCK_MONOTONIC, &ts);
@@ -416,16 +416,14 @@ Labels nvml_labels(Manager &mgr, const gfdcfg::Config &config, bool leave_attach
     t.init_ms = now() - t0;
     struct Guard {  // defer manager.Shutdown()
         Manager &m;
-        bool skip;
         PhaseTimes &t;
         double (*clock)();
         ~Guard() {
-            if (skip) return;
             double a = clock();
             m.shutdown();
             t.shutdown_ms = clock() - a;
         }
-    } guard{mgr, leave_attached, t, +now};
+    } guard{mgr, t, +now};
     Labels out;
     g_current_tables = config.current_tables;
     try {

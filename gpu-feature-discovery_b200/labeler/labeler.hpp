@@ -47,15 +47,13 @@ class Manager {
 std::unique_ptr<Manager> new_manager(const gfdcfg::Config &config);
 
 // lm.NewNVMLLabeler ... (everything between Init and the deferred Shutdown); may throw PassError.
-// leave_attached: skip the deferred Shutdown -- only for the last pass of a process that is about to exit, where
-// closing the driver handles is the kernel's job anyway (saves nvmlShutdown's 2.5 ms/GPU-ish on the way out).
 struct PhaseTimes {  // wall-clock of the NVML bracket's phases, ms (--timing)
     double init_ms = 0;      // dlopen + nvmlInit_v2
     double attach_ms = 0;    // device walk (+ per-GPU prefetch threads): where the driver attaches each GPU
     double labels_ms = 0;    // label building from the cached answers
-    double shutdown_ms = 0;  // nvmlShutdown + dlclose (0 on the last pass of a one-shot run)
+    double shutdown_ms = 0;  // nvmlShutdown + dlclose
 };
-Labels nvml_labels(Manager &mgr, const gfdcfg::Config &config, bool leave_attached = false, PhaseTimes *times = nullptr);
+Labels nvml_labels(Manager &mgr, const gfdcfg::Config &config, PhaseTimes *times = nullptr);
 // lm.NewVGPULabeler(...).Labels()
 Labels vgpu_labels(const gfdcfg::Config &config);
 // Probe entry points of libgfd_b200.so, bound lazily (probe_loader.cpp); throw PassError if the library is missing.

@@ -36,10 +36,6 @@ const char *signal_name(int s) {  // syscall.Signal.String()
     }
 }
 
-// Set when the last pass of a --oneshot / --passes run left NVML attached on purpose: start() then leaves the
-// process with _exit() right after the label file is in place instead of paying nvmlShutdown on the way out.
-bool g_fast_exit = false;
-
 // run (main.go:148-210): returns restart; throws gfdlm::PassError on error
 bool run(gfdlm::Manager &mgr, const gfdcfg::Config &config, const sigset_t &sigs) {
     struct Cleanup {  // the deferred removeOutputFile (main.go:149-156)
@@ -64,10 +60,8 @@ bool run(gfdlm::Manager &mgr, const gfdcfg::Config &config, const sigset_t &sigs
     int passes_done = 0;
     while (true) {
         double t0 = now_ms();
-        static const bool no_fast_exit = getenv("GFD_B200_NO_FAST_EXIT") != nullptr;  // measurement knob
-        const bool last_pass = !no_fast_exit && (*config.oneshot || (config.passes > 0 && passes_done + 1 >= config.passes));
         gfdlm::PhaseTimes ph;
-        gfdlm::Labels nvml = gfdlm::nvml_labels(mgr, config, last_pass, &ph);  // lm.NewLabelers: the eager NVML part
+        gfdlm::Labels nvml = gfdlm::nvml_labels(mgr, config, &ph);  // lm.NewLabelers: the eager NVML part
         double t1 = now_ms();
         gfdlm::Labels labels = timestamp;                      // lm.Merge(timestampLabeler, loopLabelers): later wins
         for (auto &kv : nvml) labels[kv.first] = kv.second;
@@ -93,7 +87,6 @@ bool run(gfdlm::Manager &mgr, const gfdcfg::Config &config, const sigset_t &sigs
             logf("timing: pass %.3f ms (nvml %.3f, vgpu %.3f, write %.3f) [init %.3f, attach %.3f, labels %.3f, shutdown %.3f]", t3 - t0, t1 - t0,
                  t2 - t1, t3 - t2, ph.init_ms, ph.attach_ms, ph.labels_ms, ph.shutdown_ms);
 
-        if (last_pass) { g_fast_exit = true; return false; }
         if (*config.oneshot) return false;
         if (config.passes > 0 && passes_done + 1 >= config.passes) return false;
         ++passes_done;
@@ -150,14 +143,7 @@ int start(const gfdcfg::ParsedFlags &flags) {
             logf("Error: %s", e.what());
             return 1;
         }
-        if (!restart) {
-            if (g_fast_exit) {  // the labels are written; the kernel closes the driver handles faster than nvmlShutdown does
-                logf("Exiting");
-                fflush(nullptr);
-                _exit(0);
-            }
-            return 0;
-        }
+        if (!restart) return 0;
     }
 }
 
