@@ -199,8 +199,18 @@ def reduce_over_ranks(pass_ms, e2e_ms, kernel_ms, probe_gbps, host_gbps, world, 
     return a[0], a[1], a[2], b[0], b[1]
 
 
+def persistence_mode():
+    """nvidia-smi's persistence_mode of GPU 0 (decides whether nvmlInit / the first handle pay the driver attach); asked
+    ONCE, before any timed region."""
+    try:
+        p = subprocess.run(["nvidia-smi", "-i", "0", "--query-gpu=persistence_mode", "--format=csv,noheader"], capture_output=True, text=True, timeout=30)
+        return p.stdout.strip().splitlines()[0].strip() if p.returncode == 0 and p.stdout.strip() else "unknown"
+    except Exception:
+        return "unknown"
+
+
 def workload_config():
-    return {"workload": "BASELINE configs[1]: B200 node, MIG strategy none, --no-timestamp, full label set from the real NVML + "
+    return {"persistence_mode": persistence_mode(), "workload": "BASELINE configs[1]: B200 node, MIG strategy none, --no-timestamp, full label set from the real NVML + "
                         "vGPU sysfs scan + atomic file write; one step = one labeling pass",
             "probe": "opt-in hbm_read_fold, %d MiB per launch (input >> 126 MB L2, so no L2 flush between iterations)" % (PROBE_BYTES >> 20),
             "parallelism": "the pass is per node: rank 0 labels all N GPUs (one host thread per GPU), no collective; probes are per-GPU replicas"}
