@@ -1,4 +1,7 @@
-"""Experiment helper: one-shot exec->exit wall-clock of the labeler with / without the fast exit, vs ref_replay."""
+"""Experiment helper: one-shot exec->exit wall-clock of the labeler (default and serial walk) vs ref_replay.
+
+profiles/r1c_e2e_breakdown_1gpu.txt was taken with an earlier build that still had the _exit() shortcut and an env knob
+to disable it ("fast exit" / "with shutdown" rows); the shortcut measured no gain and is gone, so is the knob."""
 import os, statistics, subprocess, sys, time
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 BIN = os.path.join(ROOT, "gpu-feature-discovery_b200", "gpu-feature-discovery")
@@ -17,7 +20,6 @@ def run(cmd, env=None, n=25):
     return {"median": round(statistics.median(v), 2), "min": round(min(v), 2), "inner_median": round(statistics.median(inner), 2) if inner else None}
 args = ["--oneshot", "--no-timestamp", "--timing", "-o", "/tmp/e2e_o"]
 for rep in range(2):
-    print("fast exit   ", run([BIN] + args))
-    print("with shutdown", run([BIN] + args, env=dict(os.environ, GFD_B200_NO_FAST_EXIT="1")))
+    print("default     ", run([BIN] + args))
     print("ref_replay  ", run([REPLAY, "--no-timestamp", "-o", "/tmp/e2e_r"]))
     print("serial      ", run([BIN] + args + ["--prefetch-threads=1"]))
