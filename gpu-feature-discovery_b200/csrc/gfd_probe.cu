@@ -343,8 +343,7 @@ GFD_API int gfd_hbm_copy(void *d_dst, const void *d_src, size_t bytes, void *str
 //   * a health-check or telemetry agent that shares the GPU with a job which has already claimed (nearly) all
 //     of HBM -- a cudaMalloc from the agent can fail, or can push the job itself into an out-of-memory error;
 //   * code that runs inside somebody else's memory pool discipline (a framework that forbids raw cudaMalloc
-//     because it would fragment or bypass its caching allocator);
-//   * code on a path where allocating is not allowed at all, e.g. after a stream has started capturing.
+//     because it would fragment or bypass its caching allocator).
 // For them the per-CTA partial sums live in the fixed array below.  It is part of this library's device image:
 // every GPU on which the library's kernels get loaded carries these 16 KiB from then until the process exits,
 // whether or not this entry point is ever called.

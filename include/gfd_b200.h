@@ -221,8 +221,8 @@ int gfd_hbm_copy(void *d_dst, const void *d_src, size_t bytes, void *stream);
 
 /* gfd_hbm_read_checksum without any allocation, by the caller or by the library.  No counterpart in the
  * reference.  Meant for callers that hold the data on the GPU but must not (or cannot) allocate device memory
- * when they need the checksum: an agent next to a job that already owns almost all of HBM, code living under a
- * framework's allocator rules, code past the start of a stream capture.  The per-CTA partial sums go to a fixed
+ * when they need the checksum: an agent next to a job that already owns almost all of HBM (its cudaMalloc can fail,
+ * or tip the job over), code living under a framework's allocator rules.  The per-CTA partial sums go to a fixed
  * 16 KiB array inside the library's device image (each GPU that loads the library's kernels holds it until exit).
  *   - bytes <= GFD_NOALLOC_MAX_BYTES, else GFD_ERR_SIZE_LIMIT (split the buffer at 8-byte multiples and combine
  *     the pieces: xor of xor64, sum of sum64); also GFD_ERR_SIZE_LIMIT on a GPU needing more than 1024 CTAs.

@@ -1,6 +1,5 @@
 """gfd_hbm_read_checksum_noalloc -- the checksum entry point for callers that may not allocate GPU memory
-(a monitoring agent beside a job that owns nearly all of HBM, code bound to a framework's allocator, code that
-is already past the start of a stream capture).  Its scratch is a fixed array inside the library, so the test
+(a monitoring agent beside a job that owns nearly all of HBM, code bound to a framework's allocator).  Its scratch is a fixed array inside the library, so the test
 hands it only an input buffer and a 16-byte output, and checks, through the C ABI, that the answer is bit-for-bit
 the one gfd_hbm_read_checksum gives with caller-provided scratch (integer work: the tolerance is zero).
 
