@@ -39,7 +39,9 @@ constexpr int kCopyUnroll = 2;         // 32 KiB per CTA
 constexpr uint64_t kGolden = 0x9E3779B97F4A7C15ull;
 constexpr int kMaxDevices = 64;
 
-#define CUDA_TRY(expr) do { cudaError_t e__ = (expr); if (e__ != cudaSuccess) return GFD_ERR_CUDA + (int)e__; } while (0)
+// A failed runtime call also parks its code in the runtime's "last error" slot; take it out again so that the next
+// launch's cudaGetLastError() check (e.g. the retry after an out-of-memory probe size) does not trip over it.
+#define CUDA_TRY(expr) do { cudaError_t e__ = (expr); if (e__ != cudaSuccess) { (void)cudaGetLastError(); return GFD_ERR_CUDA + (int)e__; } } while (0)
 
 struct U2 { uint64_t a, b; };
 
@@ -430,11 +432,10 @@ GFD_API int gfd_checksum_host(int cuda_device, const void *host_buf, size_t byte
     if (scope.rc) return scope.rc;
     std::lock_guard<std::mutex> lk(g_staging_mu[cuda_device]);
     Staging &s = g_staging[cuda_device];
-    if (!s.st) {
-        CUDA_TRY(cudaStreamCreateWithFlags(&s.st, cudaStreamNonBlocking));
-        CUDA_TRY(cudaMalloc(&s.d_scratch, gfd_hbm_scratch_bytes()));
-        CUDA_TRY(cudaMalloc((void **)&s.d_out, sizeof(gfd_checksum)));
-    }
+    // each piece is created on its own so that a call that failed half-way (out of memory) is completed by the next one
+    if (!s.st) CUDA_TRY(cudaStreamCreateWithFlags(&s.st, cudaStreamNonBlocking));
+    if (!s.d_scratch) CUDA_TRY(cudaMalloc(&s.d_scratch, gfd_hbm_scratch_bytes()));
+    if (!s.d_out) CUDA_TRY(cudaMalloc((void **)&s.d_out, sizeof(gfd_checksum)));
     size_t need = (bytes + 255) / 256 * 256;
     if (need > s.cap) {
         if (s.d_buf) CUDA_TRY(cudaFree(s.d_buf));

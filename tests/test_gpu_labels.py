@@ -114,6 +114,16 @@ def test_opt_in_flags_only_add_their_own_labels(B, tmp_path):
     assert "timing: pass" in err
 
 
+def test_probe_size_backs_off_when_hbm_is_short(B, tmp_path):
+    """--probe-size-mib larger than HBM: the labeler halves the buffer until it fits (down to 256 MiB) and says what it used."""
+    rc, got, err = run_cli(B, tmp_path, "--mig-strategy=none", "--probe-hbm", "--probe-size-mib=262144")  # 256 GiB > 180 GB
+    assert rc == 0, err
+    vals = dict(l.split("=") for l in got.splitlines())
+    assert 256 <= int(vals["nvidia.com/gpu.probe.hbm.size-mib"]) < 262144
+    assert 1000 < int(vals["nvidia.com/gpu.probe.hbm.read-gbps"]) < 20000
+    assert 1000 < int(vals["nvidia.com/gpu.probe.hbm.copy-gbps"]) < 20000
+
+
 def test_keep_attached_multi_pass_same_file(B, tmp_path):
     rc, base, err = run_cli(B, tmp_path, "--mig-strategy=none")
     out = os.path.join(str(tmp_path), "multi")

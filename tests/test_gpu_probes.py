@@ -183,6 +183,24 @@ def test_probe_rejects_bad_arguments(env):
             B.probe_hbm(*args[:2], warmup=args[2], iters=args[3], mode=args[4])
 
 
+def test_out_of_memory_is_an_error_and_leaves_no_stale_state(env):
+    """A probe size that cannot be allocated must come back as cudaErrorMemoryAllocation (status 100002) -- and the NEXT
+    call must work: a failed cudaMalloc also parks its code in the runtime's last-error slot, which the launch checks read."""
+    B = env.B
+    with pytest.raises(B.GfdError) as e:
+        B.probe_hbm(0, 1 << 40, warmup=1, iters=1, mode=B.PROBE_READ)  # 1 TiB
+    assert e.value.status == 100000 + 2
+    r = B.probe_hbm(0, 256 << 20, warmup=1, iters=2, mode=B.PROBE_READ)
+    o = (ctypes.c_uint64 * 2)()
+    env.orc.oracle_pattern_checksum((256 << 20) // 8, 0, o)
+    assert r.checksum.tuple() == (int(o[0]), int(o[1]))
+    with pytest.raises(B.GfdError) as e:
+        B.probe_hbm(0, 1 << 40, warmup=1, iters=1, mode=B.PROBE_COPY)
+    assert e.value.status == 100000 + 2
+    host = np.arange(1 << 16, dtype=np.uint64)
+    assert B.checksum_host(0, host.ctypes.data, host.nbytes) == oracle_checksum(env, host.view(np.uint8))
+
+
 def test_p2p_probe(env):
     """NVLink peer probe: needs >= 2 GPUs (run with gpurun --gpus 2); the pulled bytes' checksum must equal
     the pattern's closed form, i.e. every byte crossed the link intact."""
