@@ -57,7 +57,14 @@ class MigAttributes(ctypes.Structure):
 
 class VgpuInfo(ctypes.Structure):
     _fields_ = [("has_vendor_capability", ctypes.c_int), ("vendor_capability_len", ctypes.c_int), ("is_vgpu", ctypes.c_int),
-                ("host_driver_version", ctypes.c_char * 32), ("host_driver_branch", ctypes.c_char * 32)]
+                ("host_driver_version", ctypes.c_char * 32), ("host_driver_branch", ctypes.c_char * 32),
+                ("host_driver_version_len", ctypes.c_int), ("host_driver_branch_len", ctypes.c_int)]
+
+    def version(self):  # bytes, interior NULs kept (c_char arrays read as C strings would stop at the first one)
+        return ctypes.string_at(ctypes.addressof(self) + VgpuInfo.host_driver_version.offset, self.host_driver_version_len)
+
+    def branch(self):
+        return ctypes.string_at(ctypes.addressof(self) + VgpuInfo.host_driver_branch.offset, self.host_driver_branch_len)
 
 
 class Checksum(ctypes.Structure):

@@ -186,7 +186,7 @@ size_t put_go_byte(char *dst, uint8_t c) {
     return 2;
 }
 // 10 config bytes -> Go string -> strings.Trim(s, "\x00")
-void go_field(const uint8_t *p, char *out, size_t out_len) {
+int go_field(const uint8_t *p, char *out, size_t out_len) {
     char tmp[24];
     size_t n = 0;
     for (int i = 0; i < 10; i++) n += put_go_byte(tmp + n, p[i]);
@@ -197,6 +197,7 @@ void go_field(const uint8_t *p, char *out, size_t out_len) {
     if (L >= out_len) L = out_len - 1;
     memcpy(out, tmp + b, L);
     out[L] = 0;
+    return (int)L;
 }
 }  // namespace
 
@@ -248,8 +249,8 @@ GFD_API int gfd_vgpu_parse(const uint8_t *cfg, size_t len, size_t cap, gfd_vgpu_
         record = c[p];
     }
     if (record == 0 && p + 2 + 10 + 10 <= cap_len) {
-        go_field(c + p + 2, out->host_driver_version, sizeof out->host_driver_version);
-        go_field(c + p + 12, out->host_driver_branch, sizeof out->host_driver_branch);
+        out->host_driver_version_len = go_field(c + p + 2, out->host_driver_version, sizeof out->host_driver_version);
+        out->host_driver_branch_len = go_field(c + p + 12, out->host_driver_branch, sizeof out->host_driver_branch);
         return 0;
     }
     return GFD_ERR_VGPU_NO_VERSION_RECORD;

@@ -490,7 +490,9 @@ Labels vgpu_labels(const gfdcfg::Config &config) {
         if (rc == GFD_ERR_PCI_CONFIG_SHORT || (rc && !info.is_vgpu))
             fail("unable to get vGPU devices: unable to read vendor specific capability for " + p.address, rc);
         if (rc) fail("error getting vGPU device info for device " + p.address, rc);
-        if (info.is_vgpu) vgpus.push_back({p.address, info.host_driver_version, info.host_driver_branch});
+        if (info.is_vgpu)
+            vgpus.push_back({p.address, std::string(info.host_driver_version, (size_t)info.host_driver_version_len),
+                             std::string(info.host_driver_branch, (size_t)info.host_driver_branch_len)});
     }
     if (!vgpus.empty()) out["nvidia.com/vgpu.present"] = "true";
     for (const Vgpu &v : vgpus) {  // the last vGPU device wins (internal/lm/vgpu.go:46-53)

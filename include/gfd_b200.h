@@ -187,8 +187,11 @@ typedef struct gfd_vgpu_info {
     int has_vendor_capability;
     int vendor_capability_len;
     int is_vgpu;
-    char host_driver_version[32]; /* 10 config bytes, each UTF-8 encoded as Go's string(uint8) does, NUL-trimmed */
+    char host_driver_version[32]; /* 10 config bytes, each UTF-8 encoded as Go's string(uint8) does, NULs trimmed
+                                   * at both ENDS only (strings.Trim): a NUL in the middle stays, so use the lengths */
     char host_driver_branch[32];
+    int host_driver_version_len;  /* bytes in host_driver_version (a terminating NUL follows them) */
+    int host_driver_branch_len;
 } gfd_vgpu_info;
 int gfd_vgpu_parse(const uint8_t *config, size_t len, size_t cap, gfd_vgpu_info *out);
 

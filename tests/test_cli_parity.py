@@ -217,6 +217,7 @@ VGPU_EDGE = {
     "chain broken 0xff": _cfg_with_cap(bytes([0xFF, 0x00, 0x08])),
     "vendor cap, not VF": _cfg_with_cap(bytes([0x09, 0x00, 0x14, 0x01]) + bytes(16)),
     "VF, high bytes in version": _cfg_with_cap(bytes([0x09, 0x00, 0x1B, 0x56, 0x46, 0x00, 0x16]) + b"5\xe9\xff.1\x80\x00\x00\x00\x00" + b"r\xc3\xa9_00\x00\x00\x00\x00"),
+    "VF, NUL inside the version (Go keeps it; only the ends are trimmed)": _cfg_with_cap(bytes([0x09, 0x00, 0x1B, 0x56, 0x46, 0x00, 0x16]) + b"\x005\x0025.1\x00\x00\x00" + b"r5\x0025\x00\x00\x00\x00\x00"),
     "VF, two records before version": _cfg_with_cap(bytes([0x09, 0x00, 0x23, 0x56, 0x46, 0x01, 0x04, 0xAA, 0xBB, 0x02, 0x04, 0xCC, 0xDD, 0x00, 0x16]) + b"535.54.03\x00" + b"r535_00\x00\x00\x00"),
     "VF, version record truncated": _cfg_with_cap(bytes([0x09, 0x00, 0x10, 0x56, 0x46, 0x00, 0x16]) + b"535.54.03"),
     "VF, zero-length record (reference would spin)": _cfg_with_cap(bytes([0x09, 0x00, 0x1B, 0x56, 0x46, 0x05, 0x00]) + bytes(20)),
