@@ -229,6 +229,7 @@ __global__ void __launch_bounds__(64, 1) copy_tma(char *__restrict__ dst, const 
     asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
 }
 
+#ifndef HBM_SWEEP_NO_MAIN
 static cudaEvent_t e0, e1;
 template <class F>
 double time_ms(F launch, int warm = 3, int iters = 10) {
@@ -391,3 +392,4 @@ int main(int argc, char **argv) {
     }
     return 0;
 }
+#endif  // HBM_SWEEP_NO_MAIN
