@@ -52,10 +52,16 @@ __device__ __forceinline__ uint64_t evict_first_policy() {
     asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
     return pol;
 }
+// kL2Hint = false drops the policy operand: for loads that cross NVLink the hinted form costs bandwidth as soon as
+// the link carries traffic in both directions (643 vs 671 GB/s per direction, profiles/r1c_p2p_sweep_2xB200.txt).
+template <bool kL2Hint>
 __device__ __forceinline__ U2 ld_stream16(const void *p, uint64_t pol) {
     U2 r;
-    asm volatile("ld.global.nc.L1::no_allocate.L2::cache_hint.v2.u64 {%0,%1}, [%2], %3;"
-                 : "=l"(r.a), "=l"(r.b) : "l"(p), "l"(pol));
+    if (kL2Hint)
+        asm volatile("ld.global.nc.L1::no_allocate.L2::cache_hint.v2.u64 {%0,%1}, [%2], %3;"
+                     : "=l"(r.a), "=l"(r.b) : "l"(p), "l"(pol));
+    else
+        asm volatile("ld.global.nc.L1::no_allocate.v2.u64 {%0,%1}, [%2];" : "=l"(r.a), "=l"(r.b) : "l"(p));
     return r;
 }
 __device__ __forceinline__ void st_stream16(void *p, U2 v) {
@@ -89,6 +95,7 @@ __device__ __forceinline__ void block_reduce_store(Fold f, ulonglong2 *partials)
 
 // n16 = number of whole 16-byte vectors; the < 16 tail bytes are folded by the finishing kernel.
 // `tile_counter` must be 0 at launch (the host side clears it on the same stream before every launch).
+template <bool kL2Hint>
 __global__ void __launch_bounds__(kThreads, kBlocksPerSM)
 hbm_read_fold_kernel(const char *__restrict__ src, size_t n16, unsigned long long *__restrict__ tile_counter,
                      ulonglong2 *__restrict__ partials) {
@@ -108,7 +115,7 @@ hbm_read_fold_kernel(const char *__restrict__ src, size_t n16, unsigned long lon
         const char *base = src + (size_t)t * kTile * 16;
         U2 v[kUnroll];
 #pragma unroll
-        for (int j = 0; j < kUnroll; j++) v[j] = ld_stream16(base + ((size_t)j * kThreads + threadIdx.x) * 16, pol);
+        for (int j = 0; j < kUnroll; j++) v[j] = ld_stream16<kL2Hint>(base + ((size_t)j * kThreads + threadIdx.x) * 16, pol);
 #pragma unroll
         for (int j = 0; j < kUnroll; j++) f.add(v[j]);
         __syncthreads();
@@ -116,7 +123,7 @@ hbm_read_fold_kernel(const char *__restrict__ src, size_t n16, unsigned long lon
     // ragged remainder (< one tile), bounds-checked, spread over the whole grid
     for (size_t i = full_tiles * kTile + (size_t)blockIdx.x * kThreads + threadIdx.x; i < n16;
          i += (size_t)gridDim.x * kThreads)
-        f.add(ld_stream16(src + i * 16, pol));
+        f.add(ld_stream16<kL2Hint>(src + i * 16, pol));
     block_reduce_store(f, partials);
 }
 
@@ -153,6 +160,7 @@ __global__ void __launch_bounds__(256) fold_finish_kernel(const ulonglong2 *__re
 }
 
 // One 32 KiB tile per CTA; the last CTA's tile may be partial; CTA 0 also moves the < 16 tail bytes.
+template <bool kL2Hint>
 __global__ void __launch_bounds__(kCopyThreads, 2)
 hbm_copy_kernel(char *__restrict__ dst, const char *__restrict__ src, size_t n16, int tail_bytes) {
     constexpr size_t kTile = (size_t)kCopyThreads * kCopyUnroll;
@@ -161,11 +169,11 @@ hbm_copy_kernel(char *__restrict__ dst, const char *__restrict__ src, size_t n16
     if (first + kTile <= n16) {
         U2 v[kCopyUnroll];
 #pragma unroll
-        for (int j = 0; j < kCopyUnroll; j++) v[j] = ld_stream16(src + (first + (size_t)j * kCopyThreads + threadIdx.x) * 16, pol);
+        for (int j = 0; j < kCopyUnroll; j++) v[j] = ld_stream16<kL2Hint>(src + (first + (size_t)j * kCopyThreads + threadIdx.x) * 16, pol);
 #pragma unroll
         for (int j = 0; j < kCopyUnroll; j++) st_stream16(dst + (first + (size_t)j * kCopyThreads + threadIdx.x) * 16, v[j]);
     } else {
-        for (size_t i = first + threadIdx.x; i < n16; i += kCopyThreads) st_stream16(dst + i * 16, ld_stream16(src + i * 16, pol));
+        for (size_t i = first + threadIdx.x; i < n16; i += kCopyThreads) st_stream16(dst + i * 16, ld_stream16<kL2Hint>(src + i * 16, pol));
     }
     if (blockIdx.x == 0 && threadIdx.x < tail_bytes) dst[n16 * 16 + threadIdx.x] = src[n16 * 16 + threadIdx.x];
 }
@@ -244,8 +252,9 @@ int grid_for(int sms, size_t n16) {
 }
 
 // Scratch layout: [0,16) header whose first 8 bytes are the tile counter, then one ulonglong2 partial per CTA.
+// src_is_peer: d_buf is another GPU's memory reached through a peer mapping (the NVLink probe)
 int launch_read(int dev, const void *d_buf, size_t bytes, gfd_checksum *d_out, void *d_scratch, cudaStream_t st,
-                int *grid_out) {
+                int *grid_out, bool src_is_peer = false) {
     DevInfo di;
     int rc = device_info(dev, &di);
     if (rc) return rc;
@@ -255,7 +264,8 @@ int launch_read(int dev, const void *d_buf, size_t bytes, gfd_checksum *d_out, v
     auto *counter = static_cast<unsigned long long *>(d_scratch);
     auto *partials = reinterpret_cast<ulonglong2 *>(static_cast<char *>(d_scratch) + 16);
     CUDA_TRY(cudaMemsetAsync(counter, 0, 16, st));  // the scratch keeps the previous launch's counter: clear it
-    hbm_read_fold_kernel<<<grid, kThreads, 0, st>>>(static_cast<const char *>(d_buf), n16, counter, partials);
+    if (src_is_peer) hbm_read_fold_kernel<false><<<grid, kThreads, 0, st>>>(static_cast<const char *>(d_buf), n16, counter, partials);
+    else hbm_read_fold_kernel<true><<<grid, kThreads, 0, st>>>(static_cast<const char *>(d_buf), n16, counter, partials);
     CUDA_TRY(cudaGetLastError());
     fold_finish_kernel<<<1, 256, 0, st>>>(partials, grid, static_cast<const unsigned char *>(d_buf) + n16 * 16, tail, d_out);
     CUDA_TRY(cudaGetLastError());
@@ -263,14 +273,15 @@ int launch_read(int dev, const void *d_buf, size_t bytes, gfd_checksum *d_out, v
     return 0;
 }
 
-int launch_copy(int dev, void *d_dst, const void *d_src, size_t bytes, cudaStream_t st, int *grid_out) {
+int launch_copy(int dev, void *d_dst, const void *d_src, size_t bytes, cudaStream_t st, int *grid_out, bool src_is_peer = false) {
     (void)dev;
     constexpr size_t kTile = (size_t)kCopyThreads * kCopyUnroll;
     size_t n16 = bytes / 16;
     size_t tiles = (n16 + kTile - 1) / kTile;
     if (tiles < 1) tiles = 1;
     if (tiles > 0x7fffffffull) return GFD_ERR_SIZE_LIMIT;  // 64 TiB
-    hbm_copy_kernel<<<(unsigned)tiles, kCopyThreads, 0, st>>>(static_cast<char *>(d_dst), static_cast<const char *>(d_src), n16, (int)(bytes % 16));
+    if (src_is_peer) hbm_copy_kernel<false><<<(unsigned)tiles, kCopyThreads, 0, st>>>(static_cast<char *>(d_dst), static_cast<const char *>(d_src), n16, (int)(bytes % 16));
+    else hbm_copy_kernel<true><<<(unsigned)tiles, kCopyThreads, 0, st>>>(static_cast<char *>(d_dst), static_cast<const char *>(d_src), n16, (int)(bytes % 16));
     CUDA_TRY(cudaGetLastError());
     if (grid_out) *grid_out = (int)tiles;
     return 0;
@@ -320,9 +331,11 @@ GFD_API int gfd_hbm_read_checksum(const void *d_buf, size_t bytes, gfd_checksum 
     if (scratch_bytes < gfd_hbm_scratch_bytes()) return GFD_ERR_BUFFER_TOO_SMALL;
     if ((uintptr_t)d_buf % 16 || (uintptr_t)d_scratch % 16 || (uintptr_t)d_out % 8) return GFD_ERR_ALIGNMENT;
     if ((rc = device_of_pointer(d_out, &dev))) return rc;
+    int src_dev = dev;
+    if (bytes && (rc = device_of_pointer(d_buf, &src_dev))) return rc;
     DeviceScope scope(dev);
     if (scope.rc) return scope.rc;
-    return launch_read(dev, d_buf, bytes, d_out, d_scratch, static_cast<cudaStream_t>(stream), nullptr);
+    return launch_read(dev, d_buf, bytes, d_out, d_scratch, static_cast<cudaStream_t>(stream), nullptr, src_dev != dev);
 }
 
 GFD_API int gfd_hbm_copy(void *d_dst, const void *d_src, size_t bytes, void *stream) {
@@ -333,9 +346,11 @@ GFD_API int gfd_hbm_copy(void *d_dst, const void *d_src, size_t bytes, void *str
     if (!d_dst || !d_src) return GFD_ERR_BAD_ARGUMENT;
     if ((uintptr_t)d_dst % 16 || (uintptr_t)d_src % 16) return GFD_ERR_ALIGNMENT;
     if ((rc = device_of_pointer(d_dst, &dev))) return rc;
+    int src_dev = dev;
+    if ((rc = device_of_pointer(d_src, &src_dev))) return rc;
     DeviceScope scope(dev);
     if (scope.rc) return scope.rc;
-    return launch_copy(dev, d_dst, d_src, bytes, static_cast<cudaStream_t>(stream), nullptr);
+    return launch_copy(dev, d_dst, d_src, bytes, static_cast<cudaStream_t>(stream), nullptr, src_dev != dev);
 }
 
 // ---- allocation-free form of the read checksum -----------------------------------------------------------
@@ -469,7 +484,7 @@ struct Stream {
 
 // Time `iters` launches of the read/copy kernel running on `run_dev`; src may live on another device.
 int time_kernel(int run_dev, void *dst, const void *src, size_t bytes, int warmup, int iters, int mode,
-                gfd_probe_result *out) {
+                gfd_probe_result *out, bool src_is_peer = false) {
     DeviceScope scope(run_dev);
     if (scope.rc) return scope.rc;
     DevInfo di;
@@ -485,8 +500,8 @@ int time_kernel(int run_dev, void *dst, const void *src, size_t bytes, int warmu
     CUDA_TRY(cudaEventCreate(&e1.e));
     int grid = 0;
     auto once = [&]() -> int {
-        if (mode == GFD_PROBE_COPY || mode == GFD_PROBE_PUSH) return launch_copy(run_dev, dst, src, bytes, st.s, &grid);
-        return launch_read(run_dev, src, bytes, static_cast<gfd_checksum *>(d_out.p), scratch.p, st.s, &grid);
+        if (mode == GFD_PROBE_COPY || mode == GFD_PROBE_PUSH) return launch_copy(run_dev, dst, src, bytes, st.s, &grid, src_is_peer);
+        return launch_read(run_dev, src, bytes, static_cast<gfd_checksum *>(d_out.p), scratch.p, st.s, &grid, src_is_peer);
     };
     for (int i = 0; i < warmup; i++)
         if ((rc = once())) return rc;
@@ -567,7 +582,7 @@ GFD_API int gfd_probe_p2p(int src_device, int dst_device, size_t bytes, int warm
         if (s.rc) return s.rc;
         CUDA_TRY(cudaMalloc(&dst.p, bytes));
     }
-    rc = time_kernel(run_device, dst.p, src.p, bytes, warmup, iters, mode, out);
+    rc = time_kernel(run_device, dst.p, src.p, bytes, warmup, iters, mode, out, /*src_is_peer=*/mode != GFD_PROBE_PUSH);
     {
         DeviceScope s(src_device);  // free on the owning device
         if (src.p) { cudaFree(src.p); src.p = nullptr; }
@@ -598,9 +613,9 @@ int p2p_launch(int run_dev, P2PDev &me, const void *peer_src, size_t bytes, int 
     int rc;
     if (timed) CUDA_TRY(cudaEventRecord(me.e0, me.st));
     for (int i = 0; i < reps; i++) {
-        if (mode == GFD_PROBE_COPY) rc = launch_copy(run_dev, me.dst, peer_src, bytes, me.st, nullptr);
+        if (mode == GFD_PROBE_COPY) rc = launch_copy(run_dev, me.dst, peer_src, bytes, me.st, nullptr, true);
         else if (mode == GFD_PROBE_PUSH) rc = launch_copy(run_dev, const_cast<void *>(peer_src), me.src, bytes, me.st, nullptr);  // peer_src = the partner's dst
-        else rc = launch_read(run_dev, peer_src, bytes, static_cast<gfd_checksum *>(me.out), me.scratch, me.st, nullptr);
+        else rc = launch_read(run_dev, peer_src, bytes, static_cast<gfd_checksum *>(me.out), me.scratch, me.st, nullptr, true);
         if (rc) return rc;
     }
     if (timed) CUDA_TRY(cudaEventRecord(me.e1, me.st));
