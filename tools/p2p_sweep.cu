@@ -123,6 +123,9 @@ int main(int argc, char **argv) {
     });
     run("pull read  persistent LDG.128 T512 U8 x2/SM", [&](Side &me, Side &peer) { read_ldg<512, 8, 2, 2><<<me.sms * 2, 512, 0, me.st>>>(peer.src, n16, me.out); });
     run("pull read  persistent LDG.128 T512 U8 x2/SM, no hints", [&](Side &me, Side &peer) { read_ldg<512, 8, 2, 0><<<me.sms * 2, 512, 0, me.st>>>(peer.src, n16, me.out); });
+    run("pull read  persistent LDG.128 T512 U8 x2/SM, L1::no_allocate only", [&](Side &me, Side &peer) { read_ldg<512, 8, 2, 1><<<me.sms * 2, 512, 0, me.st>>>(peer.src, n16, me.out); });
+    run("pull read  persistent LDG.128 T512 U8 x2/SM, no hints (again)", [&](Side &me, Side &peer) { read_ldg<512, 8, 2, 0><<<me.sms * 2, 512, 0, me.st>>>(peer.src, n16, me.out); });
+    run("pull read  persistent LDG.128 T512 U8 x2/SM, all hints (again)", [&](Side &me, Side &peer) { read_ldg<512, 8, 2, 2><<<me.sms * 2, 512, 0, me.st>>>(peer.src, n16, me.out); });
     run("pull read  persistent LDG.128 T1024 U4 x2/SM", [&](Side &me, Side &peer) { read_ldg<1024, 4, 2, 2><<<me.sms * 2, 1024, 0, me.st>>>(peer.src, n16, me.out); });
     run("pull read  persistent LDG.128 T512 U16 x1/SM", [&](Side &me, Side &peer) { read_ldg<512, 16, 1, 2><<<me.sms, 512, 0, me.st>>>(peer.src, n16, me.out); });
     run("pull read  persistent LDG.128 T256 U8 x2/SM (half the loads in flight)", [&](Side &me, Side &peer) { read_ldg<256, 8, 2, 2><<<me.sms * 2, 256, 0, me.st>>>(peer.src, n16, me.out); });
@@ -145,6 +148,8 @@ int main(int argc, char **argv) {
     run("pull copy  one tile/CTA LDG.128 T1024 U2     [product]", [&](Side &me, Side &peer) { copy_onetile<1024, 2, 2><<<(unsigned)(n16 / 2048), 1024, 0, me.st>>>(me.dst, peer.src); });
     run("pull copy  one tile/CTA LDG.128 T512 U8", [&](Side &me, Side &peer) { copy_onetile<512, 8, 2><<<(unsigned)(n16 / 4096), 512, 0, me.st>>>(me.dst, peer.src); });
     run("pull copy  one tile/CTA LDG.256 T512 U4", [&](Side &me, Side &peer) { copy_onetile256<512, 4, 2><<<(unsigned)(n32 / 2048), 512, 0, me.st>>>(me.dst, peer.src); });
+    run("pull copy  persistent LDG.128 T512 U8 x2/SM, loads without hints", [&](Side &me, Side &peer) { copy_ldg<512, 8, 2, 0, 1><<<me.sms * 2, 512, 0, me.st>>>(me.dst, peer.src, n16); });
+    run("pull copy  persistent LDG.128 T512 U8 x2/SM, loads L1::no_allocate only", [&](Side &me, Side &peer) { copy_ldg<512, 8, 2, 1, 1><<<me.sms * 2, 512, 0, me.st>>>(me.dst, peer.src, n16); });
     run("pull copy  persistent LDG.128 T512 U8 x2/SM", [&](Side &me, Side &peer) { copy_ldg<512, 8, 2, 2, 1><<<me.sms * 2, 512, 0, me.st>>>(me.dst, peer.src, n16); });
 #define CTMA(ST, CH, WHAT, DST, SRC)                                                                              \
     {                                                                                                             \
