@@ -52,16 +52,18 @@ __device__ __forceinline__ uint64_t evict_first_policy() {
     asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
     return pol;
 }
-// kL2Hint = false drops the policy operand: for loads that cross NVLink the hinted form costs bandwidth as soon as
-// the link carries traffic in both directions (643 vs 671 GB/s per direction, profiles/r1c_p2p_sweep_2xB200.txt).
-template <bool kL2Hint>
+// kLocal = true: the source is this GPU's HBM -- no L1 allocation, evict-first in L2 (each byte is touched once).
+// kLocal = false: the source is a peer mapping (NVLink).  There the plain form is the right one: with L1::no_allocate
+// a 128-bit load costs link bandwidth as soon as the link carries traffic in both directions -- 643 vs 671 GB/s per
+// direction, same 780 one way (profiles/r1c_p2p_sweep_2xB200.txt isolates each qualifier).
+template <bool kLocal>
 __device__ __forceinline__ U2 ld_stream16(const void *p, uint64_t pol) {
     U2 r;
-    if (kL2Hint)
+    if (kLocal)
         asm volatile("ld.global.nc.L1::no_allocate.L2::cache_hint.v2.u64 {%0,%1}, [%2], %3;"
                      : "=l"(r.a), "=l"(r.b) : "l"(p), "l"(pol));
     else
-        asm volatile("ld.global.nc.L1::no_allocate.v2.u64 {%0,%1}, [%2];" : "=l"(r.a), "=l"(r.b) : "l"(p));
+        asm volatile("ld.global.nc.v2.u64 {%0,%1}, [%2];" : "=l"(r.a), "=l"(r.b) : "l"(p));
     return r;
 }
 __device__ __forceinline__ void st_stream16(void *p, U2 v) {
@@ -95,7 +97,7 @@ __device__ __forceinline__ void block_reduce_store(Fold f, ulonglong2 *partials)
 
 // n16 = number of whole 16-byte vectors; the < 16 tail bytes are folded by the finishing kernel.
 // `tile_counter` must be 0 at launch (the host side clears it on the same stream before every launch).
-template <bool kL2Hint>
+template <bool kLocal>
 __global__ void __launch_bounds__(kThreads, kBlocksPerSM)
 hbm_read_fold_kernel(const char *__restrict__ src, size_t n16, unsigned long long *__restrict__ tile_counter,
                      ulonglong2 *__restrict__ partials) {
@@ -115,7 +117,7 @@ hbm_read_fold_kernel(const char *__restrict__ src, size_t n16, unsigned long lon
         const char *base = src + (size_t)t * kTile * 16;
         U2 v[kUnroll];
 #pragma unroll
-        for (int j = 0; j < kUnroll; j++) v[j] = ld_stream16<kL2Hint>(base + ((size_t)j * kThreads + threadIdx.x) * 16, pol);
+        for (int j = 0; j < kUnroll; j++) v[j] = ld_stream16<kLocal>(base + ((size_t)j * kThreads + threadIdx.x) * 16, pol);
 #pragma unroll
         for (int j = 0; j < kUnroll; j++) f.add(v[j]);
         __syncthreads();
@@ -123,7 +125,7 @@ hbm_read_fold_kernel(const char *__restrict__ src, size_t n16, unsigned long lon
     // ragged remainder (< one tile), bounds-checked, spread over the whole grid
     for (size_t i = full_tiles * kTile + (size_t)blockIdx.x * kThreads + threadIdx.x; i < n16;
          i += (size_t)gridDim.x * kThreads)
-        f.add(ld_stream16<kL2Hint>(src + i * 16, pol));
+        f.add(ld_stream16<kLocal>(src + i * 16, pol));
     block_reduce_store(f, partials);
 }
 
@@ -160,7 +162,7 @@ __global__ void __launch_bounds__(256) fold_finish_kernel(const ulonglong2 *__re
 }
 
 // One 32 KiB tile per CTA; the last CTA's tile may be partial; CTA 0 also moves the < 16 tail bytes.
-template <bool kL2Hint>
+template <bool kLocal>
 __global__ void __launch_bounds__(kCopyThreads, 2)
 hbm_copy_kernel(char *__restrict__ dst, const char *__restrict__ src, size_t n16, int tail_bytes) {
     constexpr size_t kTile = (size_t)kCopyThreads * kCopyUnroll;
@@ -169,11 +171,11 @@ hbm_copy_kernel(char *__restrict__ dst, const char *__restrict__ src, size_t n16
     if (first + kTile <= n16) {
         U2 v[kCopyUnroll];
 #pragma unroll
-        for (int j = 0; j < kCopyUnroll; j++) v[j] = ld_stream16<kL2Hint>(src + (first + (size_t)j * kCopyThreads + threadIdx.x) * 16, pol);
+        for (int j = 0; j < kCopyUnroll; j++) v[j] = ld_stream16<kLocal>(src + (first + (size_t)j * kCopyThreads + threadIdx.x) * 16, pol);
 #pragma unroll
         for (int j = 0; j < kCopyUnroll; j++) st_stream16(dst + (first + (size_t)j * kCopyThreads + threadIdx.x) * 16, v[j]);
     } else {
-        for (size_t i = first + threadIdx.x; i < n16; i += kCopyThreads) st_stream16(dst + i * 16, ld_stream16<kL2Hint>(src + i * 16, pol));
+        for (size_t i = first + threadIdx.x; i < n16; i += kCopyThreads) st_stream16(dst + i * 16, ld_stream16<kLocal>(src + i * 16, pol));
     }
     if (blockIdx.x == 0 && threadIdx.x < tail_bytes) dst[n16 * 16 + threadIdx.x] = src[n16 * 16 + threadIdx.x];
 }
