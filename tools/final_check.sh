@@ -15,6 +15,7 @@ for rep in 1 2; do
   ./oracle/ref_replay --passes 8 --no-timestamp -o /tmp/o_r >> $OUT/replay.jsonl 2>&1
 done
 diff /tmp/o_1 /tmp/o_r > $OUT/label_diff.txt && diff /tmp/o_0 /tmp/o_r >> $OUT/label_diff.txt && echo "label diff 0 (serial, threaded vs replay)" >> $OUT/label_diff.txt
+if [ $N -ge 2 ]; then timeout 300 python tools/p2p_matrix.py --concurrent-only > $OUT/p2p_matrix_concurrent.json 2> $OUT/p2p_matrix.err; fi
 g=1
 while [ $g -le $N ]; do
   timeout 300 python bench.py --impl reference --gpus $g --steps 20 --warmup 3 > $OUT/bench_ref_$g.json 2> $OUT/bench_ref_$g.err

@@ -5,7 +5,7 @@ B = importlib.import_module("gpu-feature-discovery_b200.binding")
 n = B.cuda_device_count()
 out = {"n": n, "read": {}, "copy": {}, "push": {}}
 t0 = time.time()
-for s in range(n):
+for s in range(0 if "--concurrent-only" not in sys.argv else n, n):
     for d in range(n):
         if s == d:
             continue
