@@ -24,7 +24,7 @@ GFD_ERR_SHIM = 200000
  GFD_ERR_NOT_MIG_DEVICE, GFD_ERR_IS_MIG_DEVICE, GFD_ERR_NOT_A_MIG_HANDLE, GFD_ERR_NO_MATCHING_PROFILE,
  GFD_ERR_INVALID_GI_PROFILE, GFD_ERR_INVALID_CI_PROFILE, GFD_ERR_PCI_CONFIG_SHORT, GFD_ERR_PCI_OUT_OF_RANGE,
  GFD_ERR_VGPU_NO_VERSION_RECORD, GFD_ERR_VGPU_RECORD_LOOP, GFD_ERR_NO_GPU, GFD_ERR_PEER_ACCESS,
- GFD_ERR_SIZE_LIMIT, GFD_ERR_ALIGNMENT) = range(GFD_ERR_SHIM + 1, GFD_ERR_SHIM + 19)
+ GFD_ERR_SIZE_LIMIT, GFD_ERR_ALIGNMENT, GFD_ERR_DATA_MISMATCH) = range(GFD_ERR_SHIM + 1, GFD_ERR_SHIM + 20)
 
 BACKEND_NVML, BACKEND_CUDA, BACKEND_NULL = 0, 1, 2
 MGR_KEEP_ATTACHED = 1
@@ -38,7 +38,7 @@ SYMBOLS = [
     "gfd_call_stats", "gfd_dev_name", "gfd_dev_total_memory_mb", "gfd_dev_cuda_compute_capability",
     "gfd_dev_is_mig_capable", "gfd_dev_is_mig_enabled", "gfd_dev_mig_count", "gfd_dev_mig_get", "gfd_dev_parent",
     "gfd_dev_attributes", "gfd_dev_uuid", "gfd_mig_memory_size_gb", "gfd_mig_profile_string", "gfd_vgpu_parse",
-    "gfd_hbm_fill_pattern", "gfd_hbm_scratch_bytes", "gfd_hbm_read_checksum", "gfd_hbm_read_checksum_noalloc", "gfd_hbm_copy", "gfd_checksum_host",
+    "gfd_hbm_fill_pattern", "gfd_hbm_pattern_checksum", "gfd_hbm_scratch_bytes", "gfd_hbm_read_checksum", "gfd_hbm_read_checksum_noalloc", "gfd_hbm_copy", "gfd_checksum_host",
     "gfd_probe_hbm", "gfd_probe_p2p", "gfd_probe_p2p_matrix", "gfd_cuda_device_by_uuid", "gfd_cuda_device_count",
 ]
 
@@ -77,7 +77,7 @@ class Checksum(ctypes.Structure):
 class ProbeResult(ctypes.Structure):
     _fields_ = [("gbps", ctypes.c_double), ("ms_per_launch", ctypes.c_double), ("bytes", ctypes.c_uint64),
                 ("iters", ctypes.c_int), ("mode", ctypes.c_int), ("sm_count", ctypes.c_int), ("grid", ctypes.c_int),
-                ("block", ctypes.c_int), ("checksum", Checksum)]
+                ("block", ctypes.c_int), ("checksum", Checksum), ("expected", Checksum), ("verified", ctypes.c_int)]
 
 
 _vp, _sz, _u64, _int = ctypes.c_void_p, ctypes.c_size_t, ctypes.c_uint64, ctypes.c_int
@@ -110,6 +110,7 @@ _SIG = {
     "gfd_mig_profile_string": (_int, [_int, _int, _u64, _u64, ctypes.c_char_p, _sz]),
     "gfd_vgpu_parse": (_int, [ctypes.c_char_p, _sz, _sz, _P(VgpuInfo)]),
     "gfd_hbm_fill_pattern": (_int, [_vp, _sz, _u64, _vp]),
+    "gfd_hbm_pattern_checksum": (_int, [_sz, _u64, _vp, _vp, _sz, _vp]),
     "gfd_hbm_scratch_bytes": (_sz, []),
     "gfd_hbm_read_checksum": (_int, [_vp, _sz, _vp, _vp, _sz, _vp]),
     "gfd_hbm_read_checksum_noalloc": (_int, [_vp, _sz, _vp, _vp]),
@@ -271,6 +272,10 @@ def hbm_scratch_bytes():
 
 def hbm_fill_pattern(d_buf, nbytes, seed=0, stream=0):
     _check(lib.gfd_hbm_fill_pattern(d_buf, nbytes, seed, stream), "gfd_hbm_fill_pattern")
+
+
+def hbm_pattern_checksum(nbytes, seed, d_out, d_scratch, scratch_bytes, stream=0):
+    _check(lib.gfd_hbm_pattern_checksum(nbytes, seed, d_out, d_scratch, scratch_bytes, stream), "gfd_hbm_pattern_checksum")
 
 
 def hbm_read_checksum(d_buf, nbytes, d_out, d_scratch, scratch_bytes, stream=0):

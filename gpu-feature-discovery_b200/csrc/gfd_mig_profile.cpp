@@ -170,6 +170,7 @@ GFD_API const char *gfd_strerror(int status) {
     case GFD_ERR_PEER_ACCESS: return "peer access between the two devices is not available";
     case GFD_ERR_SIZE_LIMIT: return "size exceeds the supported maximum";
     case GFD_ERR_ALIGNMENT: return "device pointer is not 16-byte aligned";
+    case GFD_ERR_DATA_MISMATCH: return "probe data mismatch: the bytes read back are not the pattern that was written";
     default:
         snprintf(buf, sizeof buf, "unknown status %d", status);
         return buf;

@@ -194,6 +194,25 @@ fill_pattern_kernel(char *__restrict__ dst, size_t n16, int tail_bytes, uint64_t
     }
 }
 
+// What a buffer filled by fill_pattern_kernel MUST fold to, computed from the definition alone -- no memory is read.
+// Comparing it with what hbm_read_fold_kernel found in HBM (or behind NVLink) turns a bandwidth probe into a
+// write -> read verification of every byte it touched.
+__global__ void __launch_bounds__(kThreads, kBlocksPerSM)
+pattern_fold_kernel(size_t n16, int tail_bytes, uint64_t seed, ulonglong2 *__restrict__ partials) {
+    Fold f;
+    for (size_t i = (size_t)blockIdx.x * kThreads + threadIdx.x; i < n16; i += (size_t)gridDim.x * kThreads) {
+        f.add(kGolden * (2 * i + seed));
+        f.add(kGolden * (2 * i + 1 + seed));
+    }
+    if (blockIdx.x == 0 && threadIdx.x == 0 && tail_bytes > 0) {  // the ragged tail keeps the LOW bytes of its words
+        const int first = tail_bytes < 8 ? tail_bytes : 8, second = tail_bytes - first;
+        const uint64_t w0 = kGolden * (2 * n16 + seed), w1 = kGolden * (2 * n16 + 1 + seed);
+        f.add(first == 8 ? w0 : (w0 & ((1ull << (8 * first)) - 1)));
+        if (second > 0) f.add(w1 & ((1ull << (8 * second)) - 1));
+    }
+    block_reduce_store(f, partials);
+}
+
 // ---- host side --------------------------------------------------------------------------------------
 struct DevInfo { int sms = 0; bool ok = false; };
 DevInfo g_dev[kMaxDevices];
@@ -302,6 +321,24 @@ int launch_fill(int dev, void *d_buf, size_t bytes, uint64_t seed, cudaStream_t 
     return 0;
 }
 
+// expected checksum of a pattern-filled buffer; partials go to d_scratch + 16 like launch_read's
+int launch_pattern(int dev, size_t bytes, uint64_t seed, gfd_checksum *d_out, void *d_scratch, cudaStream_t st) {
+    DevInfo di;
+    int rc = device_info(dev, &di);
+    if (rc) return rc;
+    size_t n16 = bytes / 16;
+    size_t want = (n16 + kThreads - 1) / kThreads;
+    size_t cap = (size_t)di.sms * kBlocksPerSM;
+    if (cap > (size_t)kMaxBlocks) cap = kMaxBlocks;
+    int grid = (int)(want < 1 ? 1 : (want < cap ? want : cap));
+    auto *partials = reinterpret_cast<ulonglong2 *>(static_cast<char *>(d_scratch) + 16);
+    pattern_fold_kernel<<<grid, kThreads, 0, st>>>(n16, (int)(bytes % 16), seed, partials);
+    CUDA_TRY(cudaGetLastError());
+    fold_finish_kernel<<<1, 256, 0, st>>>(partials, grid, nullptr, 0, d_out);
+    CUDA_TRY(cudaGetLastError());
+    return 0;
+}
+
 }  // namespace
 
 GFD_API size_t gfd_hbm_scratch_bytes(void) { return 16 + sizeof(ulonglong2) * (size_t)kMaxBlocks; }
@@ -322,6 +359,20 @@ GFD_API int gfd_hbm_fill_pattern(void *d_buf, size_t bytes, uint64_t seed, void 
     DeviceScope scope(dev);
     if (scope.rc) return scope.rc;
     return launch_fill(dev, d_buf, bytes, seed, static_cast<cudaStream_t>(stream));
+}
+
+GFD_API int gfd_hbm_pattern_checksum(size_t bytes, uint64_t seed, gfd_checksum *d_out, void *d_scratch, size_t scratch_bytes,
+                                     void *stream) {
+    int n, dev;
+    int rc = device_count_checked(&n);
+    if (rc) return rc;
+    if (!d_out || !d_scratch) return GFD_ERR_BAD_ARGUMENT;
+    if (scratch_bytes < gfd_hbm_scratch_bytes()) return GFD_ERR_BUFFER_TOO_SMALL;
+    if ((uintptr_t)d_scratch % 16 || (uintptr_t)d_out % 8) return GFD_ERR_ALIGNMENT;
+    if ((rc = device_of_pointer(d_out, &dev))) return rc;
+    DeviceScope scope(dev);
+    if (scope.rc) return scope.rc;
+    return launch_pattern(dev, bytes, seed, d_out, d_scratch, static_cast<cudaStream_t>(stream));
 }
 
 GFD_API int gfd_hbm_read_checksum(const void *d_buf, size_t bytes, gfd_checksum *d_out, void *d_scratch,
@@ -485,8 +536,9 @@ struct Stream {
 };
 
 // Time `iters` launches of the read/copy kernel running on `run_dev`; src may live on another device.
+// READ mode also checks what was read against the pattern's definition (the source was filled with seed `seed`).
 int time_kernel(int run_dev, void *dst, const void *src, size_t bytes, int warmup, int iters, int mode,
-                gfd_probe_result *out, bool src_is_peer = false) {
+                gfd_probe_result *out, bool src_is_peer = false, uint64_t seed = 0) {
     DeviceScope scope(run_dev);
     if (scope.rc) return scope.rc;
     DevInfo di;
@@ -524,7 +576,14 @@ int time_kernel(int run_dev, void *dst, const void *src, size_t bytes, int warmu
     out->block = kThreads;
     out->ms_per_launch = (double)ms / iters;
     out->gbps = (double)bytes * iters / ((double)ms * 1e-3) / 1e9;
-    if (mode == GFD_PROBE_READ) CUDA_TRY(cudaMemcpy(&out->checksum, d_out.p, sizeof(gfd_checksum), cudaMemcpyDeviceToHost));
+    if (mode == GFD_PROBE_READ) {
+        CUDA_TRY(cudaMemcpy(&out->checksum, d_out.p, sizeof(gfd_checksum), cudaMemcpyDeviceToHost));
+        if ((rc = launch_pattern(run_dev, bytes, seed, static_cast<gfd_checksum *>(d_out.p), scratch.p, st.s))) return rc;
+        CUDA_TRY(cudaStreamSynchronize(st.s));
+        CUDA_TRY(cudaMemcpy(&out->expected, d_out.p, sizeof(gfd_checksum), cudaMemcpyDeviceToHost));
+        out->verified = (out->checksum.xor64 == out->expected.xor64 && out->checksum.sum64 == out->expected.sum64) ? 1 : 0;
+        if (!out->verified) return GFD_ERR_DATA_MISMATCH;
+    }
     return 0;
 }
 }  // namespace
@@ -644,6 +703,7 @@ GFD_API int gfd_probe_p2p_matrix(int n_devices, size_t bytes, int warmup, int it
     const int N = n_devices;
     for (int i = 0; i < N * N; i++) gbps_matrix[i] = 0.0;
     std::vector<P2PDev> dev((size_t)N);
+    std::vector<gfd_checksum> expected((size_t)N);
     auto cleanup = [&]() {
         for (int d = 0; d < N; d++) {
             DeviceScope s(d);
@@ -679,8 +739,17 @@ GFD_API int gfd_probe_p2p_matrix(int n_devices, size_t bytes, int warmup, int it
             CUDA_TRY(cudaEventCreate(&dev[d].e1));
             int frc = launch_fill(d, dev[d].src, bytes, (uint64_t)d << 40, dev[d].st);
             if (frc) return frc;
+            // what any reader of this GPU's buffer must find (READ mode checks it after every timed round)
+            if ((frc = launch_pattern(d, bytes, (uint64_t)d << 40, static_cast<gfd_checksum *>(dev[d].out), dev[d].scratch, dev[d].st))) return frc;
+            CUDA_TRY(cudaMemcpyAsync(&expected[(size_t)d], dev[d].out, sizeof(gfd_checksum), cudaMemcpyDeviceToHost, dev[d].st));
             CUDA_TRY(cudaStreamSynchronize(dev[d].st));
         }
+        auto verify = [&](int d, int p) -> int {  // GPU d has just folded GPU p's buffer into dev[d].out
+            if (mode != GFD_PROBE_READ) return 0;
+            gfd_checksum got;
+            CUDA_TRY(cudaMemcpy(&got, dev[d].out, sizeof got, cudaMemcpyDeviceToHost));
+            return (got.xor64 == expected[(size_t)p].xor64 && got.sum64 == expected[(size_t)p].sum64) ? 0 : GFD_ERR_DATA_MISMATCH;
+        };
         // circle method; an odd N gets a bye (partner == N)
         const int M = (N % 2 == 0) ? N : N + 1;
         std::vector<int> partner((size_t)M);
@@ -711,6 +780,7 @@ GFD_API int gfd_probe_p2p_matrix(int n_devices, size_t bytes, int warmup, int it
                         int erc = p2p_elapsed(d, dev[d], &ms);
                         if (erc) return erc;
                         gbps_matrix[d * N + p] = (double)bytes * iters / ((double)ms * 1e-3) / 1e9;  // row = puller, column = source
+                        if ((erc = verify(d, p))) return erc;
                     }
                 }
             }
@@ -732,6 +802,7 @@ GFD_API int gfd_probe_p2p_matrix(int n_devices, size_t bytes, int warmup, int it
                         int erc = p2p_elapsed(d, dev[d], &ms);
                         if (erc) return erc;
                         *ring_aggregate_gbps += (double)bytes * iters / ((double)ms * 1e-3) / 1e9;
+                        if ((erc = verify(d, (d + 1) % N))) return erc;
                     }
                 }
             }

@@ -56,7 +56,8 @@ enum {
     GFD_ERR_NO_GPU,               /* a probe was asked for on a host without a usable CUDA device */
     GFD_ERR_PEER_ACCESS,          /* the two devices cannot map each other's memory */
     GFD_ERR_SIZE_LIMIT,           /* request larger than a stated maximum */
-    GFD_ERR_ALIGNMENT             /* device pointer not 16-byte aligned */
+    GFD_ERR_ALIGNMENT,            /* device pointer not 16-byte aligned */
+    GFD_ERR_DATA_MISMATCH         /* a probe read back something else than the pattern it had written */
 };
 
 /* Text for any status code.  For NVML codes: nvmlErrorString() while NVML is initialised, else the fixed
@@ -210,6 +211,13 @@ typedef struct gfd_checksum {
 
 /* Fill `bytes` at d_buf with word[i] = 0x9E3779B97F4A7C15 * (i + seed) (SURVEY.md 8(d) probe input). */
 int gfd_hbm_fill_pattern(void *d_buf, size_t bytes, uint64_t seed, void *stream);
+
+/* The checksum a buffer of `bytes` filled by gfd_hbm_fill_pattern(…, seed) must have, computed on the GPU from the
+ * pattern's definition without reading any buffer (same scratch rules as gfd_hbm_read_checksum; the device is the one
+ * d_out lives on).  fill -> read_checksum == pattern_checksum is a write/read verification of the memory in between;
+ * the self-contained probes below do exactly that and fail with GFD_ERR_DATA_MISMATCH otherwise. */
+int gfd_hbm_pattern_checksum(size_t bytes, uint64_t seed, gfd_checksum *d_out, void *d_scratch, size_t scratch_bytes,
+                             void *stream);
 /* Bytes of device scratch gfd_hbm_read_checksum needs, for any input size: a 16-byte header (the tile counter the
  * CTAs draw work from; the call clears it on `stream` before launching) + one 16-byte partial sum per CTA.  The
  * scratch needs no initialisation by the caller, but two calls sharing one scratch must not overlap on the GPU. */
@@ -252,6 +260,8 @@ typedef struct gfd_probe_result {
     int sm_count;
     int grid, block;
     gfd_checksum checksum; /* of the source buffer as read by the last timed launch (read mode) */
+    gfd_checksum expected; /* what the fill pattern must fold to (read mode; gfd_hbm_pattern_checksum) */
+    int verified;          /* read mode: 1 = checksum == expected (otherwise the call returns GFD_ERR_DATA_MISMATCH) */
 } gfd_probe_result;
 int gfd_probe_hbm(int cuda_device, size_t bytes, int warmup, int iters, int mode, gfd_probe_result *out);
 /* NVLink peer probe: a kernel running on `dst_device` pulls `bytes` from a buffer on `src_device`

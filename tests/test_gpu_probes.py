@@ -101,6 +101,27 @@ def test_fill_pattern_matches_oracle(env, n, seed):
     assert not got[n:].any(), "fill wrote past the end"
 
 
+@pytest.mark.parametrize("n", [0, 1, 7, 8, 9, 15, 16, 17, 24, 31, 4097, 65536, 65536 * 7 + 9, (32 << 20) + 13])
+@pytest.mark.parametrize("seed", [0, 12345, 7 << 40])
+def test_pattern_checksum_is_the_checksum_of_the_filled_buffer(env, n, seed):
+    """gfd_hbm_pattern_checksum (no memory read) == oracle checksum of the oracle's pattern bytes == what the GPU reads back
+    from a buffer it filled: the three-way agreement the probes' write -> read verification rests on."""
+    torch, B = env.torch, env.B
+    st = torch.cuda.current_stream().cuda_stream
+    B.hbm_pattern_checksum(n, seed, env.out.data_ptr(), env.scratch.data_ptr(), env.scratch.numel(), st)
+    torch.cuda.synchronize()
+    expected = tuple(int(v) for v in env.out.cpu().numpy().view(np.uint64))
+    want = np.zeros(n, dtype=np.uint8)
+    env.orc.oracle_fill_pattern(want.ctypes.data, n, seed)
+    assert expected == oracle_checksum(env, want)
+    t = torch.zeros(max(n, 1) + 64, dtype=torch.uint8, device=env.dev)
+    B.hbm_fill_pattern(t.data_ptr(), n, seed, st)
+    assert gpu_checksum(env, t, nbytes=n) == expected
+    if n >= 8:  # one flipped bit anywhere must break the agreement
+        t[n // 2] ^= 0x10
+        assert gpu_checksum(env, t, nbytes=n) != expected
+
+
 @pytest.mark.parametrize("n", [0, 1, 15, 16, 4097, 65536, 65536 * 7 + 9, (32 << 20) + 1])
 def test_copy_is_bit_exact(env, n):
     rng = np.random.default_rng(99 + n)
@@ -170,6 +191,7 @@ def test_probe_hbm_self_contained(env):
     o = (ctypes.c_uint64 * 2)()
     env.orc.oracle_pattern_checksum(n // 8, 0, o)
     assert r.checksum.tuple() == (int(o[0]), int(o[1]))
+    assert r.verified == 1 and r.expected.tuple() == r.checksum.tuple()  # the probe checked what it read against the pattern
     assert r.bytes == n and r.iters == 5 and r.sm_count >= 100 and r.grid == r.sm_count * 2
     assert 500 < r.gbps < 20000, r.gbps
     c = B.probe_hbm(0, n, warmup=2, iters=5, mode=B.PROBE_COPY)
@@ -211,7 +233,7 @@ def test_p2p_probe(env):
     r = B.probe_p2p(0, 1, n, warmup=2, iters=5, mode=B.PROBE_READ)
     o = (ctypes.c_uint64 * 2)()
     env.orc.oracle_pattern_checksum(n // 8, 0, o)
-    assert r.checksum.tuple() == (int(o[0]), int(o[1]))
+    assert r.checksum.tuple() == (int(o[0]), int(o[1])) and r.verified == 1
     assert 50 < r.gbps < 2000, r.gbps
     c = B.probe_p2p(1, 0, n, warmup=2, iters=5, mode=B.PROBE_COPY)
     assert 50 < c.gbps < 2000, c.gbps
