@@ -536,7 +536,8 @@ struct Stream {
 };
 
 // Time `iters` launches of the read/copy kernel running on `run_dev`; src may live on another device.
-// READ mode also checks what was read against the pattern's definition (the source was filled with seed `seed`).
+// Every mode ends by checking the bytes that arrived (READ: as folded; COPY / PUSH: the destination, re-read) against the
+// pattern's definition (the source was filled with seed `seed`).
 int time_kernel(int run_dev, void *dst, const void *src, size_t bytes, int warmup, int iters, int mode,
                 gfd_probe_result *out, bool src_is_peer = false, uint64_t seed = 0) {
     DeviceScope scope(run_dev);
@@ -576,7 +577,12 @@ int time_kernel(int run_dev, void *dst, const void *src, size_t bytes, int warmu
     out->block = kThreads;
     out->ms_per_launch = (double)ms / iters;
     out->gbps = (double)bytes * iters / ((double)ms * 1e-3) / 1e9;
-    if (mode == GFD_PROBE_READ) {
+    {
+        // READ: d_out holds the fold of the last timed launch.  COPY / PUSH: fold the destination now (PUSH: it is the peer's)
+        if (mode != GFD_PROBE_READ) {
+            if ((rc = launch_read(run_dev, dst, bytes, static_cast<gfd_checksum *>(d_out.p), scratch.p, st.s, nullptr, mode == GFD_PROBE_PUSH))) return rc;
+            CUDA_TRY(cudaStreamSynchronize(st.s));
+        }
         CUDA_TRY(cudaMemcpy(&out->checksum, d_out.p, sizeof(gfd_checksum), cudaMemcpyDeviceToHost));
         if ((rc = launch_pattern(run_dev, bytes, seed, static_cast<gfd_checksum *>(d_out.p), scratch.p, st.s))) return rc;
         CUDA_TRY(cudaStreamSynchronize(st.s));
@@ -744,11 +750,19 @@ GFD_API int gfd_probe_p2p_matrix(int n_devices, size_t bytes, int warmup, int it
             CUDA_TRY(cudaMemcpyAsync(&expected[(size_t)d], dev[d].out, sizeof(gfd_checksum), cudaMemcpyDeviceToHost, dev[d].st));
             CUDA_TRY(cudaStreamSynchronize(dev[d].st));
         }
-        auto verify = [&](int d, int p) -> int {  // GPU d has just folded GPU p's buffer into dev[d].out
-            if (mode != GFD_PROBE_READ) return 0;
+        // GPU d has just received GPU `origin`'s bytes: folded into dev[d].out (READ) or stored in dev[d].dst (COPY: pulled by
+        // d; PUSH: stored there by `origin`).  Call only after EVERY stream of the round has been synchronised.
+        auto verify = [&](int d, int origin) -> int {
+            DeviceScope s(d);
+            if (s.rc) return s.rc;
+            if (mode != GFD_PROBE_READ) {
+                int vrc = launch_read(d, dev[d].dst, bytes, static_cast<gfd_checksum *>(dev[d].out), dev[d].scratch, dev[d].st, nullptr);
+                if (vrc) return vrc;
+                CUDA_TRY(cudaStreamSynchronize(dev[d].st));
+            }
             gfd_checksum got;
             CUDA_TRY(cudaMemcpy(&got, dev[d].out, sizeof got, cudaMemcpyDeviceToHost));
-            return (got.xor64 == expected[(size_t)p].xor64 && got.sum64 == expected[(size_t)p].sum64) ? 0 : GFD_ERR_DATA_MISMATCH;
+            return (got.xor64 == expected[(size_t)origin].xor64 && got.sum64 == expected[(size_t)origin].sum64) ? 0 : GFD_ERR_DATA_MISMATCH;
         };
         // circle method; an odd N gets a bye (partner == N)
         const int M = (N % 2 == 0) ? N : N + 1;
@@ -780,9 +794,13 @@ GFD_API int gfd_probe_p2p_matrix(int n_devices, size_t bytes, int warmup, int it
                         int erc = p2p_elapsed(d, dev[d], &ms);
                         if (erc) return erc;
                         gbps_matrix[d * N + p] = (double)bytes * iters / ((double)ms * 1e-3) / 1e9;  // row = puller, column = source
-                        if ((erc = verify(d, p))) return erc;
                     }
                 }
+                if (pass == 1)
+                    for (int d = 0; d < N; d++) {
+                        int p = partner[(size_t)d], vrc;
+                        if (p >= 0 && p < N && (vrc = verify(d, p))) return vrc;
+                    }
             }
         }
         if (ring_aggregate_gbps) {  // every GPU pulls from its right-hand neighbour at once
@@ -802,9 +820,13 @@ GFD_API int gfd_probe_p2p_matrix(int n_devices, size_t bytes, int warmup, int it
                         int erc = p2p_elapsed(d, dev[d], &ms);
                         if (erc) return erc;
                         *ring_aggregate_gbps += (double)bytes * iters / ((double)ms * 1e-3) / 1e9;
-                        if ((erc = verify(d, (d + 1) % N))) return erc;
                     }
                 }
+                if (pass == 1)
+                    for (int d = 0; d < N; d++) {
+                        int vrc = verify(d, mode == GFD_PROBE_PUSH ? (d + N - 1) % N : (d + 1) % N);
+                        if (vrc) return vrc;
+                    }
             }
         }
         return 0;

@@ -259,9 +259,10 @@ typedef struct gfd_probe_result {
     int mode;
     int sm_count;
     int grid, block;
-    gfd_checksum checksum; /* of the source buffer as read by the last timed launch (read mode) */
-    gfd_checksum expected; /* what the fill pattern must fold to (read mode; gfd_hbm_pattern_checksum) */
-    int verified;          /* read mode: 1 = checksum == expected (otherwise the call returns GFD_ERR_DATA_MISMATCH) */
+    gfd_checksum checksum; /* of the bytes that arrived: the source as read by the last timed launch (read mode), the
+                            * destination re-read after the last launch (copy, push) */
+    gfd_checksum expected; /* what the fill pattern must fold to (gfd_hbm_pattern_checksum) */
+    int verified;          /* 1 = checksum == expected (otherwise the call returns GFD_ERR_DATA_MISMATCH) */
 } gfd_probe_result;
 int gfd_probe_hbm(int cuda_device, size_t bytes, int warmup, int iters, int mode, gfd_probe_result *out);
 /* NVLink peer probe: a kernel running on `dst_device` pulls `bytes` from a buffer on `src_device`

@@ -196,6 +196,7 @@ def test_probe_hbm_self_contained(env):
     assert 500 < r.gbps < 20000, r.gbps
     c = B.probe_hbm(0, n, warmup=2, iters=5, mode=B.PROBE_COPY)
     assert 500 < c.gbps < 20000, c.gbps
+    assert c.verified == 1 and c.checksum.tuple() == r.checksum.tuple()  # the copy's destination was re-read and checked
 
 
 def test_probe_rejects_bad_arguments(env):
@@ -237,6 +238,8 @@ def test_p2p_probe(env):
     assert 50 < r.gbps < 2000, r.gbps
     c = B.probe_p2p(1, 0, n, warmup=2, iters=5, mode=B.PROBE_COPY)
     assert 50 < c.gbps < 2000, c.gbps
+    p = B.probe_p2p(1, 0, n, warmup=2, iters=5, mode=B.PROBE_PUSH)
+    assert c.verified == 1 and p.verified == 1 and c.checksum.tuple() == p.checksum.tuple() == r.checksum.tuple()
 
 
 def test_p2p_matrix_concurrent_tournament(env):
