@@ -356,7 +356,7 @@ def main():
     peak, peak_src = load_peaks()
     traffic = None  # dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed ncu --set full capture
     try:
-        t = json.load(open(os.path.join(ROOT, "profiles", "r1b_traffic.json")))["hbm_read_fold_kernel"]
+        t = json.load(open(os.path.join(ROOT, "profiles", "r1c_traffic.json")))["hbm_read_fold_kernel"]
         if t["bytes_per_launch"] == PROBE_BYTES:
             traffic = t["dram_bytes_read"] + t["dram_bytes_write"]
     except Exception:
@@ -379,7 +379,7 @@ def main():
         "probe_hbm_read_gbps": round(probe_total, 1),
         "probe_checksum_ok": checksum_ok,
         "roofline": {"bound": "hbm", "achieved": round(probe_gbps, 1), "peak": peak, "unit": "GB/s", "frac": round(probe_gbps / peak, 4),
-                     "traffic": traffic, "traffic_unit": "bytes per launch (ncu, profiles/r1b_ncu_full_summary.md)", "peak_source": peak_src, "kernel": "hbm_read_fold_kernel (+ 1-CTA fold_finish_kernel)",
+                     "traffic": traffic, "traffic_unit": "bytes per launch (ncu, profiles/r1c_ncu_full_summary.md)", "peak_source": peak_src, "kernel": "hbm_read_fold_kernel (+ 1-CTA fold_finish_kernel)",
                      "algorithmic_bytes_per_launch": PROBE_BYTES, "ms_per_launch": round(kernel_ms, 5),
                      "frac_of_nominal_7700": round(probe_gbps / 7700.0, 4)},
         "cpu_baseline": {"value": round(sum(rms) / len(rms), 4), "unit": "ms", "cores": 1, "kind": "port",

@@ -3,7 +3,7 @@
     ncu -i gpurun_out/prof.ncu-rep --page raw --csv > raw.csv
     python tools/ncu_summarize.py raw.csv "title line" profiles/rX_ncu_full_summary.md profiles/rX_traffic.json BYTES_PER_LAUNCH
 """
-import csv, json, sys
+import csv, json, re, sys
 
 KEEP = ["gpu__time_duration.sum", "dram__bytes_read.sum", "dram__bytes_write.sum", "gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed",
         "dram__cycles_active.avg", "lts__throughput.avg.pct_of_peak_sustained_elapsed", "sm__throughput.avg.pct_of_peak_sustained_elapsed",
@@ -29,7 +29,8 @@ def main():
             if m in col:
                 out.append("| %s | %s | %s |" % (m, r[col[m]], units[col[m]]))
         out.append("")
-        key = name.split("(")[0].split("<")[0].split("::")[-1]
+        m = re.search(r"(\w+)(?:<[^<>()]*>)?\(", name)  # "void <unnamed>::hbm_copy_kernel<1>(char *, ...)" -> hbm_copy_kernel
+        key = m.group(1) if m else name
         try:
             rd = float(r[col["dram__bytes_read.sum"]].replace(",", "")) * UNIT_SCALE[units[col["dram__bytes_read.sum"]]]
             wr = float(r[col["dram__bytes_write.sum"]].replace(",", "")) * UNIT_SCALE[units[col["dram__bytes_write.sum"]]]
@@ -40,5 +41,31 @@ def main():
     open(json_path, "w").write(json.dumps(traffic, indent=1) + "\n")
 
 
+def launches():
+    """python tools/ncu_summarize.py --launches launches.csv out.txt : per-kernel count / total / share of a
+    `--metrics gpu__time_duration.sum --csv` launch list."""
+    rows = list(csv.reader(open(sys.argv[2], errors="replace")))
+    start = next(i for i, r in enumerate(rows) if r and r[0] == "ID")
+    col = {n: i for i, n in enumerate(rows[start])}
+    agg, order = {}, []
+    for r in rows[start + 1:]:
+        if len(r) <= col["Metric Value"] or r[col["Metric Name"]] != "gpu__time_duration.sum":
+            continue
+        scale = {"ns": 1e-3, "us": 1.0, "ms": 1e3, "s": 1e6, "nsecond": 1e-3, "usecond": 1.0, "msecond": 1e3, "second": 1e6}[r[col["Metric Unit"]]]
+        us = float(r[col["Metric Value"]].replace(",", "")) * scale
+        k = r[col["Kernel Name"]]
+        if k not in agg:
+            agg[k] = [0, 0.0]
+            order.append(k)
+        agg[k][0] += 1
+        agg[k][1] += us
+    total = sum(v[1] for v in agg.values())
+    with open(sys.argv[3], "w") as f:
+        for k in order:
+            n, us = agg[k]
+            f.write("%-78s n=%3d total=%10.1f us avg=%9.1f us share=%5.1f%%\n" % (k[:78], n, us, us / n, 100 * us / total))
+        f.write("TOTAL GPU time in kernels: %.1f us over %d launches\n" % (total, sum(v[0] for v in agg.values())))
+
+
 if __name__ == "__main__":
-    main()
+    launches() if sys.argv[1] == "--launches" else main()
