@@ -180,13 +180,22 @@ hbm_copy_kernel(char *__restrict__ dst, const char *__restrict__ src, size_t n16
     if (blockIdx.x == 0 && threadIdx.x < tail_bytes) dst[n16 * 16 + threadIdx.x] = src[n16 * 16 + threadIdx.x];
 }
 
-__global__ void __launch_bounds__(kThreads, kBlocksPerSM)
+// One 32 KiB tile per CTA like the copy (the write probe times this kernel); the last tile may be partial.
+__global__ void __launch_bounds__(kCopyThreads, 2)
 fill_pattern_kernel(char *__restrict__ dst, size_t n16, int tail_bytes, uint64_t seed) {
-    for (size_t i = (size_t)blockIdx.x * kThreads + threadIdx.x; i < n16; i += (size_t)gridDim.x * kThreads) {
+    constexpr size_t kTile = (size_t)kCopyThreads * kCopyUnroll;
+    const size_t first = (size_t)blockIdx.x * kTile;
+    auto put = [&](size_t i) {
         U2 v;
         v.a = kGolden * (2 * i + seed);
         v.b = kGolden * (2 * i + 1 + seed);
         st_stream16(dst + i * 16, v);
+    };
+    if (first + kTile <= n16) {
+#pragma unroll
+        for (int j = 0; j < kCopyUnroll; j++) put(first + (size_t)j * kCopyThreads + threadIdx.x);
+    } else {
+        for (size_t i = first + threadIdx.x; i < n16; i += kCopyThreads) put(i);
     }
     if (blockIdx.x == 0 && threadIdx.x < tail_bytes) {
         uint64_t w = kGolden * (2 * n16 + (threadIdx.x >> 3) + seed);
@@ -308,16 +317,16 @@ int launch_copy(int dev, void *d_dst, const void *d_src, size_t bytes, cudaStrea
     return 0;
 }
 
-int launch_fill(int dev, void *d_buf, size_t bytes, uint64_t seed, cudaStream_t st) {
-    DevInfo di;
-    int rc = device_info(dev, &di);
-    if (rc) return rc;
+int launch_fill(int dev, void *d_buf, size_t bytes, uint64_t seed, cudaStream_t st, int *grid_out = nullptr) {
+    (void)dev;
+    constexpr size_t kTile = (size_t)kCopyThreads * kCopyUnroll;
     size_t n16 = bytes / 16;
-    size_t want = (n16 + kThreads - 1) / kThreads;
-    size_t cap = (size_t)di.sms * kBlocksPerSM * 4;
-    int grid = (int)(want < 1 ? 1 : (want < cap ? want : cap));
-    fill_pattern_kernel<<<grid, kThreads, 0, st>>>(static_cast<char *>(d_buf), n16, (int)(bytes % 16), seed);
+    size_t tiles = (n16 + kTile - 1) / kTile;
+    if (tiles < 1) tiles = 1;
+    if (tiles > 0x7fffffffull) return GFD_ERR_SIZE_LIMIT;  // 64 TiB
+    fill_pattern_kernel<<<(unsigned)tiles, kCopyThreads, 0, st>>>(static_cast<char *>(d_buf), n16, (int)(bytes % 16), seed);
     CUDA_TRY(cudaGetLastError());
+    if (grid_out) *grid_out = (int)tiles;
     return 0;
 }
 
@@ -555,6 +564,7 @@ int time_kernel(int run_dev, void *dst, const void *src, size_t bytes, int warmu
     CUDA_TRY(cudaEventCreate(&e1.e));
     int grid = 0;
     auto once = [&]() -> int {
+        if (mode == GFD_PROBE_WRITE) return launch_fill(run_dev, dst, bytes, seed, st.s, &grid);
         if (mode == GFD_PROBE_COPY || mode == GFD_PROBE_PUSH) return launch_copy(run_dev, dst, src, bytes, st.s, &grid, src_is_peer);
         return launch_read(run_dev, src, bytes, static_cast<gfd_checksum *>(d_out.p), scratch.p, st.s, &grid, src_is_peer);
     };
@@ -599,14 +609,16 @@ GFD_API int gfd_probe_hbm(int cuda_device, size_t bytes, int warmup, int iters, 
     int rc = device_count_checked(&n);
     if (rc) return rc;
     if (!out || cuda_device < 0 || cuda_device >= n || bytes == 0 || iters <= 0 || warmup < 0 ||
-        (mode != GFD_PROBE_READ && mode != GFD_PROBE_COPY))
+        (mode != GFD_PROBE_READ && mode != GFD_PROBE_COPY && mode != GFD_PROBE_WRITE))
         return GFD_ERR_BAD_ARGUMENT;
     DeviceScope scope(cuda_device);
     if (scope.rc) return scope.rc;
     Buf src, dst;
-    CUDA_TRY(cudaMalloc(&src.p, bytes));
-    if (mode == GFD_PROBE_COPY) CUDA_TRY(cudaMalloc(&dst.p, bytes));
-    if ((rc = launch_fill(cuda_device, src.p, bytes, 0, nullptr))) return rc;
+    if (mode != GFD_PROBE_WRITE) {
+        CUDA_TRY(cudaMalloc(&src.p, bytes));
+        if ((rc = launch_fill(cuda_device, src.p, bytes, 0, nullptr))) return rc;
+    }
+    if (mode != GFD_PROBE_READ) CUDA_TRY(cudaMalloc(&dst.p, bytes));
     CUDA_TRY(cudaDeviceSynchronize());
     rc = time_kernel(cuda_device, dst.p, src.p, bytes, warmup, iters, mode, out);
     if (rc) return rc;

@@ -519,7 +519,7 @@ Labels probe_labels(const gfdcfg::Config &config) {
             *used = bytes;
             return e;
         };
-        double rmin = 1e30, cmin = 1e30;
+        double rmin = 1e30, cmin = 1e30, wmin = 1e30;
         size_t size_min = (size_t)config.probe_bytes, used = 0;
         for (int d = 0; d < n; d++) {
             gfd_probe_result r;
@@ -528,9 +528,12 @@ Labels probe_labels(const gfdcfg::Config &config) {
             size_min = std::min(size_min, used);
             if ((rc = run(d, (size_t)config.probe_bytes / 2, GFD_PROBE_COPY, &r, &used))) fail("HBM copy probe failed on GPU " + std::to_string(d), rc);
             cmin = std::min(cmin, r.gbps);
+            if ((rc = run(d, (size_t)config.probe_bytes, GFD_PROBE_WRITE, &r, &used))) fail("HBM write probe failed on GPU " + std::to_string(d), rc);
+            wmin = std::min(wmin, r.gbps);
         }
         out["nvidia.com/gpu.probe.hbm.read-gbps"] = std::to_string((long long)rmin);
         out["nvidia.com/gpu.probe.hbm.copy-gbps"] = std::to_string((long long)cmin);
+        out["nvidia.com/gpu.probe.hbm.write-gbps"] = std::to_string((long long)wmin);
         out["nvidia.com/gpu.probe.hbm.size-mib"] = std::to_string((long long)(size_min >> 20));
     }
     if (config.probe_nvlink && n >= 2) {

@@ -250,7 +250,12 @@ int gfd_hbm_read_checksum_noalloc(const void *d_buf, size_t bytes, gfd_checksum 
 int gfd_checksum_host(int cuda_device, const void *host_buf, size_t bytes, gfd_checksum *out);
 
 /* Self-contained probes: allocate, fill, warm up, time `iters` launches with CUDA events, free. */
-enum gfd_probe_mode { GFD_PROBE_READ = 0, GFD_PROBE_COPY = 1, GFD_PROBE_PUSH = 2 /* p2p only: the source GPU stores into the peer */ };
+enum gfd_probe_mode {
+    GFD_PROBE_READ = 0,
+    GFD_PROBE_COPY = 1,
+    GFD_PROBE_PUSH = 2, /* p2p only: the source GPU stores into the peer */
+    GFD_PROBE_WRITE = 3 /* hbm only: the fill kernel is what gets timed (bytes written / time) */
+};
 typedef struct gfd_probe_result {
     double gbps;           /* algorithmic bytes (bytes, or 2*bytes for copy over HBM; bytes per direction for p2p) / time */
     double ms_per_launch;

@@ -108,7 +108,7 @@ def test_opt_in_flags_only_add_their_own_labels(B, tmp_path):
     assert base_lines <= got_lines
     extra = sorted(got_lines - base_lines)
     assert [l.split("=")[0] for l in extra] == ["nvidia.com/gpu.probe.hbm.copy-gbps", "nvidia.com/gpu.probe.hbm.read-gbps",
-                                                "nvidia.com/gpu.probe.hbm.size-mib"]
+                                                "nvidia.com/gpu.probe.hbm.size-mib", "nvidia.com/gpu.probe.hbm.write-gbps"]
     vals = dict(l.split("=") for l in extra)
     assert 1000 < int(vals["nvidia.com/gpu.probe.hbm.read-gbps"]) < 20000
     assert "timing: pass" in err
@@ -122,6 +122,7 @@ def test_probe_size_backs_off_when_hbm_is_short(B, tmp_path):
     assert 256 <= int(vals["nvidia.com/gpu.probe.hbm.size-mib"]) < 262144
     assert 1000 < int(vals["nvidia.com/gpu.probe.hbm.read-gbps"]) < 20000
     assert 1000 < int(vals["nvidia.com/gpu.probe.hbm.copy-gbps"]) < 20000
+    assert 1000 < int(vals["nvidia.com/gpu.probe.hbm.write-gbps"]) < 20000
 
 
 def test_keep_attached_multi_pass_same_file(B, tmp_path):

@@ -197,6 +197,11 @@ def test_probe_hbm_self_contained(env):
     c = B.probe_hbm(0, n, warmup=2, iters=5, mode=B.PROBE_COPY)
     assert 500 < c.gbps < 20000, c.gbps
     assert c.verified == 1 and c.checksum.tuple() == r.checksum.tuple()  # the copy's destination was re-read and checked
+    w = B.probe_hbm(0, n, warmup=2, iters=5, mode=B.PROBE_WRITE)  # the fill kernel timed; what it wrote is re-read and checked
+    assert 500 < w.gbps < 20000, w.gbps
+    assert w.verified == 1 and w.checksum.tuple() == r.checksum.tuple()
+    w = B.probe_hbm(0, (64 << 20) + 40, warmup=1, iters=2, mode=B.PROBE_WRITE)  # ragged: partial last tile + 8 tail bytes
+    assert w.verified == 1
 
 
 def test_probe_rejects_bad_arguments(env):
