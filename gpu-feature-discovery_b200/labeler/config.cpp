@@ -50,7 +50,7 @@ static const std::vector<FlagDef> &flag_defs() {
          "the path to a config file as an alternative to command line options or environment variables", false},
         // ---- new, opt-in; absent from the reference ----
         {"probe-hbm", {}, Kind::Bool, "false", {"GFD_PROBE_HBM"},
-         "[b200, opt-in] measure HBM bandwidth per GPU with an sm_100a streaming kernel and add nvidia.com/gpu.probe.hbm.* labels", true},
+         "[b200, opt-in] measure HBM read / copy / write bandwidth per GPU with sm_100a streaming kernels (data verified) and add nvidia.com/gpu.probe.hbm.* labels", true},
         {"probe-nvlink", {}, Kind::Bool, "false", {"GFD_PROBE_NVLINK"},
          "[b200, opt-in] measure peer-to-peer NVLink bandwidth per GPU pair and add nvidia.com/gpu.probe.nvlink.* labels", true},
         {"probe-size-mib", {}, Kind::Int, "4096", {"GFD_PROBE_SIZE_MIB"}, "[b200, opt-in] probe buffer size in MiB", true},

@@ -249,7 +249,8 @@ int gfd_hbm_read_checksum_noalloc(const void *d_buf, size_t bytes, gfd_checksum 
  * them there, bring the 16-byte result back.  Staging memory is allocated on first use and cached. */
 int gfd_checksum_host(int cuda_device, const void *host_buf, size_t bytes, gfd_checksum *out);
 
-/* Self-contained probes: allocate, fill, warm up, time `iters` launches with CUDA events, free. */
+/* Self-contained probes: allocate, fill, warm up, time `iters` launches with CUDA events, verify the bytes that arrived
+ * against the pattern (GFD_ERR_DATA_MISMATCH otherwise), free.  gfd_probe_hbm takes READ, COPY or WRITE. */
 enum gfd_probe_mode {
     GFD_PROBE_READ = 0,
     GFD_PROBE_COPY = 1,
