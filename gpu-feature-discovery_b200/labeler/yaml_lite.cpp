@@ -19,8 +19,8 @@ const Value *Value::get_fold(const std::string &key) const {
     for (const auto &kv : obj) {
         if (kv.first.size() != key.size()) continue;
         bool eq = true;
-        for (size_t i = 0; i < key.size() && eq; i++)
-            eq = std::tolower((unsigned char)kv.first[i]) == std::tolower((unsigned char)key[i]);
+        for (size_t c = 0; c < key.size() && eq; c++)
+            eq = std::tolower((unsigned char)kv.first[c]) == std::tolower((unsigned char)key[c]);
         if (eq) return &kv.second;
     }
     return nullptr;

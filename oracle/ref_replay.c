@@ -10,7 +10,7 @@
  *     one dlopen/dlsym/dlclose per IsMigCapable / IsMigEnabled            V/nvlib/nvlib/device/device.go:326-338
  *     GetProfile per MIG-device wrapper (cache per wrapper only)          V/nvlib/nvlib/device/mig_device.go:52-148
  *     Shutdown = nvmlShutdown + dlclose                                    init.go:60-72
- * and builds the same labels (internal/lm/*.go) and writes them the same way (internal/lm/labels.go:68-114).
+ * and builds the same labels (internal/lm/ *.go) and writes them the same way (internal/lm/labels.go:68-114).
  * It has none of Go's runtime cost (cgo transitions, GC, scheduler), so its time is a LOWER bound on the
  * reference's.  tests/test_ref_replay.py checks (a) its NVML call trace equals the Python oracle's call for
  * call and (b) its label file equals the oracle's, on every fixture.
