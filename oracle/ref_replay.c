@@ -492,7 +492,7 @@ static int nvml_labels(labels_t *out, const char *strategy, const char *machine_
                 qsort(groups, (size_t)ng, sizeof *groups, groupcmp);
                 for (int i = 0; i < ng; i++) {
                     char res[160];
-                    snprintf(res, sizeof res, "nvidia.com/mig-%s", groups[i].name);
+                    snprintf(res, sizeof res, "nvidia.com/mig-%.140s", groups[i].name);
                     if ((rc = mig_resource_labels(&mig, res, groups[i].dev, groups[i].name, groups[i].count))) { fail("failed to construct labeler", rc); goto done; }
                 }
             }
@@ -627,11 +627,11 @@ static int write_file(const labels_t *l, const char *path) {
     char *body = malloc(cap);
     for (int i = 0; i < l->n; i++) off += (size_t)sprintf(body + off, "%s=%s\n", l->e[i].k, l->e[i].v);
     if (!path[0]) { fwrite(body, 1, off, stdout); free(body); return 0; }
-    char abs[PATH_MAX];
+    char abs[2 * PATH_MAX + 2];
     if (path[0] == '/') snprintf(abs, sizeof abs, "%s", path);
     else { char cwd[PATH_MAX]; if (!getcwd(cwd, sizeof cwd)) return 1; snprintf(abs, sizeof abs, "%s/%s", cwd, path); }
     char *slash = strrchr(abs, '/');
-    char dir[PATH_MAX], tmp[PATH_MAX];
+    char dir[sizeof abs + 16], tmp[sizeof abs + 32];
     snprintf(dir, sizeof dir, "%.*s/gfd-tmp", (int)(slash - abs), abs);
     if (mkdir(dir, 0777) != 0 && errno != EEXIST) { free(body); return fail("failed to create temporary directory", errno); }
     snprintf(tmp, sizeof tmp, "%s/gfd-XXXXXX", dir);
