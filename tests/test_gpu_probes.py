@@ -211,6 +211,34 @@ def test_probe_rejects_bad_arguments(env):
             B.probe_hbm(*args[:2], warmup=args[2], iters=args[3], mode=args[4])
 
 
+@pytest.mark.parametrize("n", [0, 1, 15, 16, 17, 4097, 32767, 32768, 32769, 65535, 65536, 65537, 3 * 65536 + 5, (8 << 20) + 13])
+def test_no_store_outside_the_buffer_and_all_paths_agree(env, n):
+    """Guard bands around every written buffer (compute-sanitizer is not available on the pool): fill and copy must leave the
+    canaries on both sides alone, and fill -> read, copy -> read, the pattern's definition and the no-alloc read must agree."""
+    torch, B, G = env.torch, env.B, 4096
+    st = torch.cuda.current_stream().cuda_stream
+
+    def guarded():
+        t = torch.full((n + 2 * G,), 0xA5, dtype=torch.uint8, device=env.dev)
+        return t, t[G:G + max(n, 1)]
+
+    tb, buf = guarded()
+    td, dst = guarded()
+    B.hbm_fill_pattern(buf.data_ptr(), n, 7, st)
+    a = gpu_checksum(env, buf, nbytes=n)
+    B.hbm_copy(dst.data_ptr(), buf.data_ptr(), n, st)
+    b = gpu_checksum(env, dst, nbytes=n)
+    B.hbm_pattern_checksum(n, 7, env.out.data_ptr(), env.scratch.data_ptr(), env.scratch.numel(), st)
+    torch.cuda.synchronize()
+    c = tuple(int(v) for v in env.out.cpu().numpy().view(np.uint64))
+    assert B.lib.gfd_hbm_read_checksum_noalloc(buf.data_ptr(), n, env.out.data_ptr(), st) == 0
+    torch.cuda.synchronize()
+    d = tuple(int(v) for v in env.out.cpu().numpy().view(np.uint64))
+    assert a == b == c == d
+    for t in (tb, td):
+        assert bool((t[:G] == 0xA5).all()) and bool((t[G + n:] == 0xA5).all()), "a kernel stored outside its buffer"
+
+
 def test_out_of_memory_is_an_error_and_leaves_no_stale_state(env):
     """A probe size that cannot be allocated must come back as cudaErrorMemoryAllocation (status 100002) -- and the NEXT
     call must work: a failed cudaMalloc also parks its code in the runtime's last-error slot, which the launch checks read."""
