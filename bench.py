@@ -155,6 +155,7 @@ def reference_arm(args, rank, world):
     r = replay_passes(total, out)
     ms = r["ms"][args.warmup:]
     value = sum(ms) / len(ms)
+    spread = {"median": round(statistics.median(ms), 4), "min": round(min(ms), 4), "max": round(max(ms), 4)}
     e2e = []
     for i in range(total):  # same definition as the product arm's e2e: exec -> exit of a one-shot run + reading the file
         t0 = time.perf_counter()
@@ -179,7 +180,7 @@ def reference_arm(args, rank, world):
         "e2e": {"value": round(e2e_ms, 4), "unit": "ms", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0, "mean": round(sum(e2e) / len(e2e), 4),
                 "note": "MEDIAN over the K steps of exec->exit of a one-shot oracle/ref_replay run + reading the label file (process spawns on "
                         "this box have 40-270 ms outliers for either arm: profiles/r1c_e2e_context_1gpu.txt)"},
-        "gpu_launches": 0,
+        "gpu_launches": 0, "labeling_pass_ms_spread": spread,
     }
     print(json.dumps(line), flush=True)
     return 0
@@ -256,10 +257,11 @@ def main():
     # that runs it -- once, over all N GPUs, with the labeler's own per-GPU host threads -- while the other ranks
     # wait at the barrier.  N copies of a node-level daemon hammering one driver would measure contention, not GFD.
     barrier()
-    pass_ms, product_text, phases = 0.0, "", {}
+    pass_ms, product_text, phases, pass_stats = 0.0, "", {}, {}
     if rank == 0:
         ms = product_passes(B.BIN_PATH, args.warmup + args.steps, out_file)[args.warmup:]
         pass_ms = sum(ms) / len(ms)
+        pass_stats = {"median": round(statistics.median(ms), 4), "min": round(min(ms), 4), "max": round(max(ms), 4)}
         phases = dict(PHASES)
         product_text = open(out_file).read()
     barrier()
@@ -375,6 +377,7 @@ def main():
         "label_diff": {"vs_cpu_baseline": diff_lines(product_text, replay_text), "vs_oracle_pynvml": diff_lines(product_text, oracle_text),
                        "labels": len(product_text.splitlines())},
         "labeling_pass_phases_ms": phases,
+        "labeling_pass_ms_spread": pass_stats,  # `value` is the mean over the K steps (the contract); a shared host makes single passes jump
         "labeling_pass_ms_keep_attached": round(sum(keep) / len(keep), 4),
         "probe_hbm_read_gbps": round(probe_total, 1),
         "probe_checksum_ok": checksum_ok,
