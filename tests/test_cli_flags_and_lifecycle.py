@@ -300,3 +300,25 @@ def test_oneshot_keeps_file_and_leaves_tmp_dir(tmp_path):
 def test_unwritable_output_directory_is_an_error(tmp_path):
     rc, _, se = run_cli(["--oneshot", "-o", "/proc/nope/gfd"], env=base_env(tmp_path))
     assert rc == 1 and "error writing file '/proc/nope/gfd'" in se
+
+
+def test_daemon_memory_does_not_grow_with_the_number_of_passes(tmp_path):
+    """A DaemonSet pod runs for months: every Init..Shutdown bracket must give back what it took (device objects, cached
+    answers, the dlopen handle).  Peak RSS after 1500 passes of a 56-MIG-device node must equal the peak after 30, give or
+    take allocator noise.  (`make asan` + detect_leaks over 200 passes is the byte-exact version of this check.)"""
+    fix = use_node(N.nodes()["c4_single_8x7x1g23"], str(tmp_path))
+    empty = os.path.join(str(tmp_path), "pci")
+    os.makedirs(empty)
+    peaks = []
+    for passes in (30, 1500):
+        script = ("import resource, subprocess, sys; "
+                  "p = subprocess.run(sys.argv[1:], stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL); "
+                  "print(p.returncode, resource.getrusage(resource.RUSAGE_CHILDREN).ru_maxrss)")
+        env = dict(os.environ, LD_LIBRARY_PATH=B.FAKE_NVML_DIR + ":" + os.environ.get("LD_LIBRARY_PATH", ""), GFD_FAKE_NVML=fix,
+                   GFD_B200_PCI_DEVICES_ROOT=empty)
+        out = subprocess.run(["python3", "-c", script, binary_path(), "--passes", str(passes), "--sleep-interval", "0s", "--mig-strategy=single",
+                              "--no-timestamp", "-o", os.path.join(str(tmp_path), "out")], env=env, capture_output=True, text=True, timeout=300)
+        rc, kb = out.stdout.split()
+        assert rc == "0", out.stderr
+        peaks.append(int(kb))
+    assert peaks[1] - peaks[0] < 1024, "peak RSS grew by %d KiB between 30 and 1500 passes" % (peaks[1] - peaks[0])
