@@ -19,7 +19,9 @@
  * Threading: one thread may drive a manager start to finish (the reference is single-goroutine);
  * distinct managers may be used from distinct threads.  Handles (gfd_dev*) are owned by their manager
  * and are valid from gfd_init() until gfd_shutdown() -- the same lifetime NVML gives device handles
- * inside the reference's Init()...defer Shutdown() bracket (internal/lm/nvml.go:30-33).
+ * inside the reference's Init()...defer Shutdown() bracket (internal/lm/nvml.go:30-33).  A handle used after
+ * gfd_shutdown() is answered with GFD_ERR_NOT_INITIALIZED; once the manager is initialised AGAIN (or freed) old
+ * handles dangle and must not be used -- fetch new ones with gfd_device_get().
  *
  * The library has NO link-time dependency on libnvidia-ml or libcuda: both are dlopen()ed on first
  * use, so it loads on a CPU-only host (BASELINE config #1).  GPU queries have no CPU fallback: where
