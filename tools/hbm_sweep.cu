@@ -229,6 +229,44 @@ __global__ void __launch_bounds__(64, 1) copy_tma(char *__restrict__ dst, const 
     asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
 }
 
+template <int T, int U, int BPS, int LH, int SH>
+__global__ void __launch_bounds__(T, BPS) copy_onetile_h(char *__restrict__ dst, const char *__restrict__ src) {
+    constexpr size_t kTile = (size_t)T * U;
+    const uint64_t pol = policy_evict_first();
+    const size_t off = (size_t)blockIdx.x * kTile * 16;
+    U2 v[U];
+#pragma unroll
+    for (int j = 0; j < U; j++) v[j] = ld16<LH>(src + off + ((size_t)j * T + threadIdx.x) * 16, pol);
+#pragma unroll
+    for (int j = 0; j < U; j++) st16<SH>(dst + off + ((size_t)j * T + threadIdx.x) * 16, v[j], pol);
+}
+// 256-bit loads and stores, one tile per CTA
+template <int T, int U, int BPS>
+__global__ void __launch_bounds__(T, BPS) copy_onetile_256(char *__restrict__ dst, const char *__restrict__ src) {
+    constexpr size_t kTile = (size_t)T * U;
+    const size_t off = (size_t)blockIdx.x * kTile * 32;
+    uint64_t a[U], b[U], c[U], d[U];
+#pragma unroll
+    for (int j = 0; j < U; j++)
+        asm volatile("ld.global.nc.L1::no_allocate.v4.u64 {%0,%1,%2,%3}, [%4];" : "=l"(a[j]), "=l"(b[j]), "=l"(c[j]), "=l"(d[j]) : "l"(src + off + ((size_t)j * T + threadIdx.x) * 32));
+#pragma unroll
+    for (int j = 0; j < U; j++)
+        asm volatile("st.global.L1::no_allocate.v4.u64 [%0], {%1,%2,%3,%4};" ::"l"(dst + off + ((size_t)j * T + threadIdx.x) * 32), "l"(a[j]), "l"(b[j]), "l"(c[j]), "l"(d[j]) : "memory");
+}
+// write-only: one tile per CTA
+template <int T, int U, int BPS, int SH>
+__global__ void __launch_bounds__(T, BPS) write_onetile(char *__restrict__ dst) {
+    constexpr size_t kTile = (size_t)T * U;
+    const uint64_t pol = policy_evict_first();
+    const size_t first = (size_t)blockIdx.x * kTile;
+#pragma unroll
+    for (int j = 0; j < U; j++) {
+        size_t i = first + (size_t)j * T + threadIdx.x;
+        U2 v{0x9E3779B97F4A7C15ull * (2 * i), 0x9E3779B97F4A7C15ull * (2 * i + 1)};
+        st16<SH>(dst + i * 16, v, pol);
+    }
+}
+
 #ifndef HBM_SWEEP_NO_MAIN
 static cudaEvent_t e0, e1;
 template <class F>
@@ -275,6 +313,33 @@ int main(int argc, char **argv) {
     {                                                                                                            \
         double ms = time_ms([&] { read_ldg<T, U, BPS, HINT><<<sms * BPS * MULT, T>>>(src, n16, out); });        \
         printf("read  ldg T=%4d U=%2d BPS=%d hint=%d grid=%5d : %8.1f GB/s  %.4f ms\n", T, U, BPS, HINT, sms * BPS * MULT, gb / ms * 1e3, ms); \
+    }
+    if (argc > 2 && argv[2][0] == '4') {  // fourth stage: cache qualifiers and widths on the one-tile copy; write-only shapes
+#define CH(T, U, BPS, LH, SH)                                                                                    \
+    {                                                                                                            \
+        size_t tiles = n16 / ((size_t)T * U);                                                                    \
+        double ms = time_ms([&] { copy_onetile_h<T, U, BPS, LH, SH><<<(unsigned)tiles, T>>>(dst, src); });       \
+        printf("copy  onetile T=%4d U=%2d BPS=%d lh=%d sh=%d : %8.1f GB/s (r+w) %.4f ms\n", T, U, BPS, LH, SH, 2 * gb / ms * 1e3, ms); \
+    }
+        for (int rep = 0; rep < 2; rep++) {
+            CH(1024, 2, 2, 2, 1) CH(1024, 2, 2, 0, 0) CH(1024, 2, 2, 1, 1) CH(1024, 2, 2, 0, 1) CH(1024, 2, 2, 2, 0) CH(1024, 2, 2, 2, 2) CH(1024, 2, 2, 1, 0) CH(1024, 2, 2, 1, 2)
+            CH(1024, 1, 2, 2, 1) CH(512, 2, 4, 2, 1) CH(512, 1, 4, 2, 1) CH(256, 2, 8, 2, 1) CH(1024, 4, 2, 2, 1)
+#define C256(T, U, BPS)                                                                                          \
+    {                                                                                                            \
+        size_t tiles = (bytes / 32) / ((size_t)T * U);                                                           \
+        double ms = time_ms([&] { copy_onetile_256<T, U, BPS><<<(unsigned)tiles, T>>>(dst, src); });             \
+        printf("copy  onetile256 T=%4d U=%2d BPS=%d       : %8.1f GB/s (r+w) %.4f ms\n", T, U, BPS, 2 * gb / ms * 1e3, ms); \
+    }
+            C256(1024, 1, 2) C256(512, 2, 4) C256(1024, 2, 2) C256(512, 1, 4) C256(256, 2, 8)
+#define WR(T, U, BPS, SH)                                                                                        \
+    {                                                                                                            \
+        size_t tiles = n16 / ((size_t)T * U);                                                                    \
+        double ms = time_ms([&] { write_onetile<T, U, BPS, SH><<<(unsigned)tiles, T>>>(dst); });                 \
+        printf("write onetile T=%4d U=%2d BPS=%d sh=%d      : %8.1f GB/s %.4f ms\n", T, U, BPS, SH, gb / ms * 1e3, ms); \
+    }
+            WR(1024, 2, 2, 1) WR(1024, 2, 2, 0) WR(1024, 2, 2, 2) WR(512, 4, 4, 1) WR(1024, 4, 2, 1) WR(1024, 1, 2, 1) WR(256, 8, 8, 1)
+        }
+        return 0;
     }
     if (argc > 2 && argv[2][0] == '3') {  // third stage: one tile per CTA, and dynamic tile counter
         unsigned long long *slots;
