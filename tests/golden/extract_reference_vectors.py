@@ -384,6 +384,21 @@ def main():
         json.dump(goldens, f, indent=1)
         f.write("\n")
 
+    # --- the node labels the reference's README shows for a real A100 node (README.md:137-151): the only place the
+    # reference documents VALUES that come out of the NVML boundary (two-part driver version -> empty rev, CUDA version
+    # split, memory in MiB, family from compute capability, product from the device name)
+    readme = read("README.md").split("\n")
+    first = next(i for i, l in enumerate(readme) if l.strip() == "labels:")
+    labels = {}
+    for l in readme[first + 1:]:
+        m = re.match(r'\s+(nvidia\.com/[\w.\-]+): "?([^"]*)"?\s*$', l)
+        if not m:
+            break
+        labels[m.group(1)] = m.group(2)
+    with open(os.path.join(OUT, "readme_node_example.json"), "w") as f:
+        json.dump({"cite": "README.md:%d-%d" % (first + 2, first + 1 + len(labels)), "labels": labels}, f, indent=1, sort_keys=True)
+        f.write("\n")
+
     n = sum(len(v["cases"]) for v in vectors.values() if isinstance(v, dict) and "cases" in v)
     print("wrote %d lm cases, %d init-matrix rows, 2 vGPU blobs" % (n, len(matrix)))
 

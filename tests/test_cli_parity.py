@@ -271,3 +271,28 @@ def test_current_tables_profile_names():
         mb = {1: 22912, 2: 45824, 4: 91648}[int(want.split("g.")[0][-1])] if "1g.45gb" not in want else 45824
         with pytest.raises(B.GfdError):
             B.mig_profile_string(gi, ci, mb, MIBS)  # the plain C-ABI call keeps the reference's tables
+
+
+# ---- the node the reference's README shows (README.md:138-150) ----------------------------------------------------
+def test_readme_node_example(tmp_path):
+    """The only VALUES the reference documents for the NVML boundary: an A100 node's labels in its README.  A node with that
+    GPU (device name, 39538 MiB, cc 8.0), that two-part driver version and CUDA 11.1 must give every label shown there --
+    from the oracle and from the binary.  Differences that are the README's age, not ours: the listing predates
+    `gpu.replicas` / `mig.capable` / `mig.strategy` (extra labels are fine) and shows the machine name before
+    machine-type.go:37 turned spaces into dashes."""
+    ex = json.load(open(os.path.join(os.path.dirname(__file__), "golden", "readme_node_example.json")))["labels"]
+    node = M.NodeFix(driver_version="%s.%s" % (ex["nvidia.com/cuda.driver.major"], ex["nvidia.com/cuda.driver.minor"]),
+                     cuda_driver_version=int(ex["nvidia.com/cuda.runtime.major"]) * 1000 + int(ex["nvidia.com/cuda.runtime.minor"]) * 10,
+                     gpus=[M.GpuFix(name=ex["nvidia.com/gpu.product"], memory_total=int(ex["nvidia.com/gpu.memory"]) << 20,
+                                    cc=(int(ex["nvidia.com/gpu.compute.major"]), int(ex["nvidia.com/gpu.compute.minor"])), mig_mode=(0, 0))])
+    machine = ex["nvidia.com/gpu.machine"].encode() + b"\n"
+    want, _ = oracle_pass(node, "none", machine=machine)
+    rc, got, stderr, _ = cli_pass(tmp_path, node, "none", machine=machine)
+    assert rc == 0 and got == want, stderr
+    lines = dict(l.split("=", 1) for l in got.splitlines())
+    for k, v in ex.items():
+        if k == "nvidia.com/gfd.timestamp":
+            continue
+        if k == "nvidia.com/gpu.machine":
+            v = v.replace(" ", "-")
+        assert lines[k] == v, (k, lines.get(k), v)
