@@ -399,6 +399,24 @@ def main():
         json.dump({"cite": "README.md:%d-%d" % (first + 2, first + 1 + len(labels)), "labels": labels}, f, indent=1, sort_keys=True)
         f.write("\n")
 
+    # --- how the reference's own manifests start the binary: container args + env of every static manifest / job template
+    manifests = {}
+    rels = ["gpu-feature-discovery-daemonset.yaml", "gpu-feature-discovery-job.yaml.template"]
+    rels += sorted("deployments/static/" + f for f in os.listdir(os.path.join(REF, "deployments", "static"))
+                   if f.startswith("gpu-feature-discovery") and f.endswith((".yaml", ".template")))
+    for rel in rels:
+        src = read(rel)
+        env = re.findall(r'- name: ([A-Z][A-Z0-9_]*)\s*\n\s*value: "?([^"\n]*)"?', src)
+        args = []
+        m = re.search(r"\n\s*args:\s*\n((?:\s*- .*\n)+)", src)
+        if m:
+            args = [a.strip()[2:].strip().strip('"') for a in m.group(1).strip("\n").split("\n")]
+        mounts = re.findall(r'mountPath: "?([^"\n]+)"?', src)
+        manifests[rel] = {"env": dict(env), "args": args, "mount_paths": mounts}
+    with open(os.path.join(OUT, "manifests.json"), "w") as f:
+        json.dump({"cite": "container spec of each manifest under the reference root", "manifests": manifests}, f, indent=1, sort_keys=True)
+        f.write("\n")
+
     n = sum(len(v["cases"]) for v in vectors.values() if isinstance(v, dict) and "cases" in v)
     print("wrote %d lm cases, %d init-matrix rows, 2 vGPU blobs" % (n, len(matrix)))
 

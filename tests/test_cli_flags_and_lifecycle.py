@@ -322,3 +322,29 @@ def test_daemon_memory_does_not_grow_with_the_number_of_passes(tmp_path):
         assert rc == "0", out.stderr
         peaks.append(int(kb))
     assert peaks[1] - peaks[0] < 1024, "peak RSS grew by %d KiB between 30 and 1500 passes" % (peaks[1] - peaks[0])
+
+
+MANIFESTS = json.load(open(os.path.join(os.path.dirname(__file__), "golden", "manifests.json")))["manifests"]
+
+
+@pytest.mark.parametrize("rel", sorted(MANIFESTS))
+def test_started_the_way_the_reference_manifests_start_it(rel, tmp_path):
+    """Every manifest the reference ships (static DaemonSets, the Job template) starts the binary with some args + env:
+    the drop-in must accept exactly those, come up with the strategy they ask for, and write where they mount features.d."""
+    m = MANIFESTS[rel]
+    fix = use_node(N.nodes()["c4_single_8x7x1g23"], str(tmp_path))
+    out = os.path.join(str(tmp_path), "gfd")
+    env = dict(m["env"], GFD_FAKE_NVML=fix, GFD_OUTPUT_FILE=out, GFD_NO_TIMESTAMP="true")
+    args = list(m["args"])
+    if "--oneshot" not in args:
+        env["GFD_ONESHOT"] = "true"  # the DaemonSets loop for ever; one pass is enough here
+    rc, _, se = run_cli(args, env=env)
+    assert rc == 0, se
+    cfg = json.loads(re.search(r"Running with config:\n(\{.*?\n\})\n", se, re.S).group(1))
+    assert cfg["flags"]["migStrategy"] == m["env"].get("MIG_STRATEGY", "none")
+    labels = dict(l.split("=", 1) for l in open(out).read().splitlines())
+    assert labels.get("nvidia.com/mig.strategy", "none") == m["env"].get("MIG_STRATEGY", "none") or m["env"].get("MIG_STRATEGY", "none") == "none"
+    # the default output file lives in the directory the manifests mount for NFD
+    rc, so, _ = run_cli(["--help"])
+    default_out = re.search(r"--output-file.*?\(default: \"?([^\")]+)\"?\)", so, re.S).group(1)
+    assert os.path.dirname(default_out) in [p.rstrip("/") for p in m["mount_paths"]]
