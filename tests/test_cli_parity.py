@@ -188,6 +188,7 @@ def test_vgpu_reference_blobs_in_sysfs(tmp_path):
     assert "nvidia.com/vgpu.present=true\n" in got
     assert "nvidia.com/vgpu.host-driver-version=%s\n" % VG["expect"]["host_driver_version"] in got
     assert "nvidia.com/vgpu.host-driver-branch=%s\n" % VG["expect"]["host_driver_branch"] in got
+    _check_result(got, "expected-output-vgpu.txt", is_vgpu=True)  # the vGPU half of TestRunOneshot's checkResult
 
 
 def test_vgpu_unprivileged_short_config_fails_the_pass(tmp_path):
@@ -296,3 +297,81 @@ def test_readme_node_example(tmp_path):
         if k == "nvidia.com/gpu.machine":
             v = v.replace(" ", "-")
         assert lines[k] == v, (k, lines.get(k), v)
+
+
+# ---- the reference's run()-level tests (cmd/gpu-feature-discovery/main_test.go, mig_test.go) through the BINARY ------
+# The reference drives run() with mock devices; the binary has no mock seam, so each scenario is rebuilt as a simulated NVML
+# node with the same shape (an A100-like GPU called MOCKMODEL; MIG devices 3g.20gb / 1g.5gb) and checked the way
+# checkResult (main_test.go:403-435) checks: every output line must match >= 1 regex of the scenario's expected-output file,
+# plus the scenario's own spot assertions wherever they do not depend on the mocks' made-up memory sizes.
+_REGEX = json.load(open(os.path.join(os.path.dirname(__file__), "golden", "expected_output_regexes.json")))["files"]
+
+
+def _check_result(text, expected_file, is_vgpu=False):
+    import re
+    regexps = [re.compile(l) for l in _REGEX[expected_file]]
+    for line in text.rstrip("\n").split("\n"):
+        if ("vgpu" in line) != is_vgpu:
+            continue
+        assert any(r.search(line) for r in regexps), "line does not match any regexp of %s: %s" % (expected_file, line)
+
+
+def _mock_like(mig=None, enabled=None):
+    g = N.a100_gpu(mig=mig)
+    g.name = "MOCKMODEL"
+    if enabled is not None:
+        g.mig_mode = (1, 1) if enabled else (0, 0)
+    return M.NodeFix(gpus=[g])
+
+
+def _run_binary(tmp_path, node, strategy, timestamp=False):
+    rc, got, stderr, out = cli_pass(tmp_path, node, strategy, machine=b"product-name\n",
+                                    extra_args=["--no-timestamp=false"] if timestamp else [])
+    assert rc == 0, stderr
+    return got, dict(l.split("=", 1) for l in got.splitlines())
+
+
+def test_binary_run_oneshot(tmp_path):  # TestRunOneshot, main_test.go:91-134 (its vGPU half: test_vgpu_reference_blobs_in_sysfs)
+    got, labels = _run_binary(tmp_path, _mock_like(), "none", timestamp=True)
+    _check_result(got, "expected-output.txt")
+    assert len(labels) == 15 and labels["nvidia.com/gpu.machine"] == "product-name" and "nvidia.com/gfd.timestamp" in labels
+
+
+def test_binary_run_with_no_timestamp(tmp_path):  # TestRunWithNoTimestamp, main_test.go:136-180
+    got, labels = _run_binary(tmp_path, _mock_like(), "none")
+    _check_result(got, "expected-output.txt")
+    assert "nvidia.com/gfd.timestamp" not in labels
+
+
+def test_binary_mig_strategy_none(tmp_path):  # TestMigStrategyNone, mig_test.go:17-72
+    got, labels = _run_binary(tmp_path, _mock_like(mig=[(2, 2), (2, 2)]), "none")
+    _check_result(got, "expected-output-mig-none.txt")
+    assert labels["nvidia.com/gpu.count"] == "1" and labels["nvidia.com/gpu.product"] == "MOCKMODEL"
+
+
+def test_binary_mig_strategy_single_no_mig_devices(tmp_path):  # TestMigStrategySingleForNoMigDevices, mig_test.go:74-126
+    got, labels = _run_binary(tmp_path, _mock_like(), "single")
+    _check_result(got, "expected-output-mig-single.txt")
+    assert labels["nvidia.com/mig.strategy"] == "single" and labels["nvidia.com/gpu.count"] == "1"
+    assert labels["nvidia.com/gpu.product"] == "MOCKMODEL"
+
+
+def test_binary_mig_strategy_single_mig_disabled(tmp_path):  # TestMigStrategySingleForMigDeviceMigDisabled, mig_test.go:128-186
+    got, labels = _run_binary(tmp_path, _mock_like(mig=[(2, 2), (2, 2)], enabled=False), "single")
+    _check_result(got, "expected-output-mig-single.txt")
+    assert labels["nvidia.com/gpu.count"] == "1" and labels["nvidia.com/gpu.product"] == "MOCKMODEL"
+
+
+def test_binary_mig_strategy_single(tmp_path):  # TestMigStrategySingle, mig_test.go:188-245
+    got, labels = _run_binary(tmp_path, _mock_like(mig=[(2, 2), (2, 2)]), "single")
+    _check_result(got, "expected-output-mig-single.txt")
+    assert labels["nvidia.com/mig.strategy"] == "single" and labels["nvidia.com/gpu.count"] == "2"
+    assert labels["nvidia.com/gpu.product"] == "MOCKMODEL-MIG-3g.20gb"
+
+
+def test_binary_mig_strategy_mixed(tmp_path):  # TestMigStrategyMixed, mig_test.go:247-306
+    got, labels = _run_binary(tmp_path, _mock_like(mig=[(2, 2), (0, 0)]), "mixed")
+    _check_result(got, "expected-output-mig-mixed.txt")
+    assert labels["nvidia.com/mig.strategy"] == "mixed" and labels["nvidia.com/gpu.count"] == "1"
+    assert labels["nvidia.com/gpu.product"] == "MOCKMODEL"
+    assert "nvidia.com/mig-3g.20gb.count" in labels and "nvidia.com/mig-1g.5gb.count" in labels
