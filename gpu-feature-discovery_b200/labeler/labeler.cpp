@@ -13,6 +13,7 @@
 #include <cstring>
 #include <fstream>
 #include <sstream>
+#include <thread>
 
 #include "go_compat.hpp"
 
@@ -519,17 +520,33 @@ Labels probe_labels(const gfdcfg::Config &config) {
             *used = bytes;
             return e;
         };
+        // The GPUs are independent (replicas): one host thread per GPU runs its three probes; results and the
+        // first error (lowest GPU index) are folded afterwards on this thread.
+        struct PerGpu { int rc = 0; const char *what = ""; double read = 0, copy = 0, write = 0; size_t used = 0; };
+        std::vector<PerGpu> res((size_t)n);
+        std::vector<std::thread> pool;
+        for (int d = 0; d < n; d++)
+            pool.emplace_back([&, d] {
+                PerGpu &g = res[(size_t)d];
+                gfd_probe_result r;
+                size_t used = 0;
+                if ((g.rc = run(d, (size_t)config.probe_bytes, GFD_PROBE_READ, &r, &g.used))) { g.what = "HBM read probe failed on GPU "; return; }
+                g.read = r.gbps;
+                if ((g.rc = run(d, (size_t)config.probe_bytes / 2, GFD_PROBE_COPY, &r, &used))) { g.what = "HBM copy probe failed on GPU "; return; }
+                g.copy = r.gbps;
+                if ((g.rc = run(d, (size_t)config.probe_bytes, GFD_PROBE_WRITE, &r, &used))) { g.what = "HBM write probe failed on GPU "; return; }
+                g.write = r.gbps;
+            });
+        for (auto &t : pool) t.join();
         double rmin = 1e30, cmin = 1e30, wmin = 1e30;
-        size_t size_min = (size_t)config.probe_bytes, used = 0;
+        size_t size_min = (size_t)config.probe_bytes;
         for (int d = 0; d < n; d++) {
-            gfd_probe_result r;
-            if ((rc = run(d, (size_t)config.probe_bytes, GFD_PROBE_READ, &r, &used))) fail("HBM read probe failed on GPU " + std::to_string(d), rc);
-            rmin = std::min(rmin, r.gbps);
-            size_min = std::min(size_min, used);
-            if ((rc = run(d, (size_t)config.probe_bytes / 2, GFD_PROBE_COPY, &r, &used))) fail("HBM copy probe failed on GPU " + std::to_string(d), rc);
-            cmin = std::min(cmin, r.gbps);
-            if ((rc = run(d, (size_t)config.probe_bytes, GFD_PROBE_WRITE, &r, &used))) fail("HBM write probe failed on GPU " + std::to_string(d), rc);
-            wmin = std::min(wmin, r.gbps);
+            const PerGpu &g = res[(size_t)d];
+            if (g.rc) fail(g.what + std::to_string(d), g.rc);
+            rmin = std::min(rmin, g.read);
+            cmin = std::min(cmin, g.copy);
+            wmin = std::min(wmin, g.write);
+            size_min = std::min(size_min, g.used);
         }
         out["nvidia.com/gpu.probe.hbm.read-gbps"] = std::to_string((long long)rmin);
         out["nvidia.com/gpu.probe.hbm.copy-gbps"] = std::to_string((long long)cmin);
