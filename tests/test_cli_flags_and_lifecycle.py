@@ -306,6 +306,8 @@ def test_daemon_memory_does_not_grow_with_the_number_of_passes(tmp_path):
     """A DaemonSet pod runs for months: every Init..Shutdown bracket must give back what it took (device objects, cached
     answers, the dlopen handle).  Peak RSS after 1500 passes of a 56-MIG-device node must equal the peak after 30, give or
     take allocator noise.  (`make asan` + detect_leaks over 200 passes is the byte-exact version of this check.)"""
+    if "san" in os.environ.get("GFD_TEST_BINDIR", ""):
+        pytest.skip("sanitizer builds keep freed memory in quarantine: RSS says nothing there (LSan checks leaks instead)")
     fix = use_node(N.nodes()["c4_single_8x7x1g23"], str(tmp_path))
     empty = os.path.join(str(tmp_path), "pci")
     os.makedirs(empty)
