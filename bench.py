@@ -215,7 +215,10 @@ def workload_config():
     return {"persistence_mode": persistence_mode(), "workload": "BASELINE configs[1]: B200 node, MIG strategy none, --no-timestamp, full label set from the real NVML + "
                         "vGPU sysfs scan + atomic file write; one step = one labeling pass",
             "probe": "opt-in hbm_read_fold, %d MiB per launch (input >> 126 MB L2, so no L2 flush between iterations)" % (PROBE_BYTES >> 20),
-            "parallelism": "the pass is per node: rank 0 labels all N GPUs (one host thread per GPU), no collective; probes are per-GPU replicas"}
+            "parallelism": "the pass is per node: rank 0 labels all N GPUs (one host thread per GPU), no collective; probes are per-GPU replicas",
+            "multi_rank_note": "with N > 1 the waiting ranks hold CUDA contexts on their GPUs (parked in a host-side gloo barrier), and a GPU that is "
+                               "already held open makes nvmlInit_v2 cheaper (profiles/r1c_pass_spread_8xB200.txt); the reference arm's other ranks "
+                               "exit at once, so its node is idle: the like-for-like comparison is the N = 1 line"}
 
 
 def main():
