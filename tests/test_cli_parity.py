@@ -267,7 +267,6 @@ def test_current_tables_profile_names():
     MIBS = 183359 * 1024 * 1024
     cases = {(8, 1): "2g.45gb+me", (9, 0): "1g.45gb", (0xA, 0): "1g.23gb+gfx", (0xB, 1): "2g.45gb+gfx", (0xC, 3): "4g.90gb+gfx",
              (0xD, 0): "1g.23gb-me", (0xE, 0): "1c.2g.45gb-me", (0xF, 7): "1g.23gb+me.all", (0x10, 1): "2g.45gb+me.all"}
-    import ctypes
     for (gi, ci), want in cases.items():
         mb = {1: 22912, 2: 45824, 4: 91648}[int(want.split("g.")[0][-1])] if "1g.45gb" not in want else 45824
         with pytest.raises(B.GfdError):

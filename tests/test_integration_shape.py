@@ -5,12 +5,10 @@ the reference's tests/expected-output.txt (15 labels, MIG strategy none).  CPU: 
 import os
 import re
 import signal
-import time
 
 import pytest
 
-import nodes as N
-from shimutil import B, use_node
+from shimutil import B
 import test_cli_flags_and_lifecycle as L
 
 GOLDEN = os.path.join(os.path.dirname(__file__), "golden")

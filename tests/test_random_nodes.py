@@ -9,9 +9,8 @@ import os
 
 from hypothesis import HealthCheck, given, settings, strategies as st
 
-import nodes as N
 from oracle import gfd_oracle as O, nvml_model as M
-from shimutil import B, ShimManager, load_fake, run_cli, use_node
+from shimutil import ShimManager, load_fake, run_cli, use_node
 
 MIB = 1024 * 1024
 MODELS = [("NVIDIA B200", 183359 * MIB, (10, 0)), ("NVIDIA A100-SXM4-40GB", 40536 * MIB, (8, 0)), ("NVIDIA H100 80GB HBM3", 81559 * MIB, (9, 0)),

@@ -3,7 +3,6 @@
 Both sides see the same `.nvmlfix` node: the oracle through RawNvml (Python), the shim through the fake
 libnvidia-ml.so.1 (C).  The oracle's label builders are run over BOTH managers, so any difference in a name,
 a profile string, an attribute, a count or in *whether an error occurs* shows up as a label diff."""
-import os
 
 import pytest
 

@@ -2,7 +2,7 @@
 
 profiles/r1c_e2e_breakdown_1gpu.txt was taken with an earlier build that still had the _exit() shortcut and an env knob
 to disable it ("fast exit" / "with shutdown" rows); the shortcut measured no gain and is gone, so is the knob."""
-import os, statistics, subprocess, sys, time
+import os, statistics, subprocess, time
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 BIN = os.path.join(ROOT, "gpu-feature-discovery_b200", "gpu-feature-discovery")
 REPLAY = os.path.join(ROOT, "oracle", "ref_replay")

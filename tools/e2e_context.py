@@ -1,6 +1,6 @@
 """Experiment helper: does the one-shot exec->exit time depend on what the PARENT process holds (torch imported, a CUDA
 context, a 4 GiB allocation, a just-terminated nvidia-smi poller)?  Prints mean / median / max of 30 runs per case."""
-import os, statistics, subprocess, sys, time
+import os, statistics, subprocess, time
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 BIN = os.path.join(ROOT, "gpu-feature-discovery_b200", "gpu-feature-discovery")
 REPLAY = os.path.join(ROOT, "oracle", "ref_replay")

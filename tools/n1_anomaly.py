@@ -1,6 +1,6 @@
 """Experiment helper: on a multi-GPU box, does the labeling pass time depend on what the PARENT holds (nothing / a CUDA
 context on GPU 0, as bench.py --gpus 1 does) or is the spread host noise?  Prints per-pass ms, phases and /proc/loadavg."""
-import os, statistics, subprocess, sys, time
+import os, statistics, subprocess
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 BIN = os.path.join(ROOT, "gpu-feature-discovery_b200", "gpu-feature-discovery")
 def passes(tag, extra=()):
