@@ -11,7 +11,8 @@ file write).  The reference has no GPU compute on this path, so:
   metric / value   labeling_pass_ms: steady-state wall-clock of one pass inside the running labeler
                    (gpu-feature-discovery --passes K+W --sleep-interval 0s --timing; mean of the last K).
   e2e              the same work as a user gets it: exec -> exit of `gpu-feature-discovery --oneshot
-                   --no-timestamp -o FILE` plus reading FILE back.  The path moves no tensor data, so
+                   --no-timestamp -o FILE` plus reading FILE back (median over the K runs; the mean is kept beside
+                   it: process spawns on a shared host have 40-270 ms outliers).  The path moves no tensor data, so
                    h2d/d2h bytes are 0 and stated as such; `e2e_probe_host` carries the host-buffer form of the
                    probe kernel (pinned host -> HBM -> checksum -> 16 bytes back) for completeness.
   label_diff       lines that differ between the product's file and (a) the CPU baseline's file, (b) the Python
@@ -24,6 +25,8 @@ file write).  The reference has no GPU compute on this path, so:
 `--impl reference` times that replay alone (rank 0 only under torchrun) and prints the same line shape.
 N > 1: the pass is per node and does not shard across ranks, so rank 0 runs it once over all N GPUs (the labeler's own
 per-GPU host threads are the multi-GPU path) while every rank probes its own GPU (replicas); probe GB/s is the sum.
+Barriers between the regions go over a gloo group: a rank waiting in an NCCL barrier spins a kernel on its GPU, which
+is one of the GPUs rank 0's pass is attaching to.
 """
 import argparse
 import ctypes
