@@ -253,12 +253,25 @@ def main():
         # Barriers go over a gloo (TCP) group: an NCCL barrier is a kernel that SPINS on every waiting rank's GPU (and a
         # polling host thread), and rank 0's labeling passes attach to exactly those GPUs through NVML meanwhile --
         # measured on 2 GPUs: pass median 50 ms with the other rank parked in an NCCL barrier, 21-30 ms without.
-        host_group = dist.new_group(backend="gloo")
+        os.environ.setdefault("GLOO_SOCKET_IFNAME", "lo")  # one node: loopback always exists, the hostname may not resolve
+        try:
+            host_group = dist.new_group(backend="gloo")
+        except Exception as e:  # no gloo transport: fall back to a barrier through the node's file system
+            print("bench: gloo group unavailable (%s); using a file barrier" % e, file=sys.stderr)
+    token = [tempfile.mkdtemp(prefix="gfd-bench-barrier-") if rank == 0 else None]
+    if world > 1 and host_group is None:
+        dist.broadcast_object_list(token, src=0)
+    barrier_no = [0]
 
     def barrier():
         torch.cuda.synchronize()
-        if world > 1:
+        if world > 1 and host_group is not None:
             dist.barrier(group=host_group)
+        elif world > 1:
+            barrier_no[0] += 1
+            open(os.path.join(token[0], "%d.%d" % (barrier_no[0], rank)), "w").close()
+            while not all(os.path.exists(os.path.join(token[0], "%d.%d" % (barrier_no[0], r))) for r in range(world)):
+                time.sleep(0.001)
         torch.cuda.synchronize()
 
     tmp = tempfile.mkdtemp(prefix="gfd-bench-r%d-" % rank)
