@@ -255,6 +255,8 @@ def main():
         # measured on 2 GPUs: pass median 50 ms with the other rank parked in an NCCL barrier, 21-30 ms without.
         os.environ.setdefault("GLOO_SOCKET_IFNAME", "lo")  # one node: loopback always exists, the hostname may not resolve
         try:
+            if os.environ.get("GFD_BENCH_FILE_BARRIER"):  # test knob: exercise the fallback
+                raise RuntimeError("forced by GFD_BENCH_FILE_BARRIER")
             host_group = dist.new_group(backend="gloo")
         except Exception as e:  # no gloo transport: fall back to a barrier through the node's file system
             print("bench: gloo group unavailable (%s); using a file barrier" % e, file=sys.stderr)
