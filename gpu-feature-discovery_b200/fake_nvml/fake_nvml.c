@@ -249,6 +249,20 @@ EXPORT nvmlReturn_t nvmlDeviceGetName(nvmlDevice_t d, char *name, unsigned int l
     return rc;
 }
 
+/* For pynvml-driven checkers only (tests/test_gpu_labels.py and tools/mig_hw_stage.py can then be dry-run against a simulated node);
+ * the reference's call sequence contains neither symbol, so the traces of the parity tests are unaffected. */
+EXPORT nvmlReturn_t nvmlInitWithFlags(unsigned int flags) { (void)flags; return nvmlInit_v2(); }
+EXPORT nvmlReturn_t nvmlDeviceGetUUID(nvmlDevice_t d, char *uuid, unsigned int length) {
+    gpu_t *g = gpu_of(d); mig_t *m = mig_of(d);
+    if (!g) { trace("nvmlDeviceGetUUID"); return NVML_ERROR_INVALID_ARGUMENT; }
+    nvmlReturn_t rc = rc_for("nvmlDeviceGetUUID", g, m);
+    if (uuid && length) {
+        if (m) snprintf(uuid, length, "MIG-00000000-0000-0000-%04x-%012x", g->index, m->slot);
+        else snprintf(uuid, length, "GPU-00000000-0000-0000-0000-%012x", g->index);
+    }
+    return rc;
+}
+
 EXPORT nvmlReturn_t nvmlDeviceGetMemoryInfo(nvmlDevice_t d, nvmlMemory_t *mem) {
     gpu_t *g = gpu_of(d); mig_t *m = mig_of(d);
     if (!g) { trace("nvmlDeviceGetMemoryInfo"); return NVML_ERROR_INVALID_ARGUMENT; }

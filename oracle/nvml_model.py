@@ -429,6 +429,15 @@ class PynvmlRaw:
     def _str(v):
         return v.decode() if isinstance(v, bytes) else v
 
+    @staticmethod
+    def _v1(fn):
+        """The reference binds the v1-struct symbols (V/go-nvml/nvml/nvml.go:2354,2364); current pynvml defaults to the `...V`
+        (v2 struct) entry points, so ask for version 1 where the wrapper takes a version."""
+        import inspect
+        if "version" in inspect.signature(fn).parameters:
+            return lambda *a: fn(*a, version=1)
+        return fn
+
     def init(self): return self._call("nvmlInit_v2", self.nv.nvmlInit)
     def shutdown(self): return self._call("nvmlShutdown", self.nv.nvmlShutdown)
 
@@ -497,12 +506,12 @@ class PynvmlRaw:
         return rc, ({"id": int(v.id), "profile_id": int(v.profileId)} if rc == 0 else None)
 
     def device_get_gpu_instance_profile_info(self, h, idx):
-        rc, v = self._call("nvmlDeviceGetGpuInstanceProfileInfo", self.nv.nvmlDeviceGetGpuInstanceProfileInfo, h, idx)
+        rc, v = self._call("nvmlDeviceGetGpuInstanceProfileInfo", self._v1(self.nv.nvmlDeviceGetGpuInstanceProfileInfo), h, idx)
         return rc, ({"id": int(v.id), "slice_count": int(v.sliceCount), "memory_size_mb": int(v.memorySizeMB)} if rc == 0 else None)
 
     def gpu_instance_get_compute_instance_profile_info(self, gi, idx, eng):
         rc, v = self._call("nvmlGpuInstanceGetComputeInstanceProfileInfo",
-                           self.nv.nvmlGpuInstanceGetComputeInstanceProfileInfo, gi, idx, eng)
+                           self._v1(self.nv.nvmlGpuInstanceGetComputeInstanceProfileInfo), gi, idx, eng)
         return rc, ({"id": int(v.id), "slice_count": int(v.sliceCount)} if rc == 0 else None)
 
 
