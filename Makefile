@@ -36,6 +36,7 @@ TARGETS += $(DEMO)
 all: $(TARGETS)
 
 $(LIB): $(LIB_SRCS) $(CSRC)/gfd_internal.h include/gfd_b200.h
+	@mkdir -p build
 	$(NVCC) $(NVCCFLAGS) -shared -cudart static -x cu $(LIB_SRCS) -o $@ -ldl -lpthread 2> build/ptxas_$(notdir $@).log || (cat build/ptxas_$(notdir $@).log; false)
 	@grep -E "registers|spill" build/ptxas_$(notdir $@).log | sort | uniq -c | head -20
 

@@ -38,7 +38,7 @@ SYMBOLS = [
     "gfd_call_stats", "gfd_dev_name", "gfd_dev_total_memory_mb", "gfd_dev_cuda_compute_capability",
     "gfd_dev_is_mig_capable", "gfd_dev_is_mig_enabled", "gfd_dev_mig_count", "gfd_dev_mig_get", "gfd_dev_parent",
     "gfd_dev_attributes", "gfd_dev_uuid", "gfd_mig_memory_size_gb", "gfd_mig_profile_string", "gfd_vgpu_parse",
-    "gfd_hbm_fill_pattern", "gfd_hbm_pattern_checksum", "gfd_hbm_scratch_bytes", "gfd_hbm_read_checksum", "gfd_hbm_read_checksum_noalloc", "gfd_hbm_copy", "gfd_checksum_host",
+    "gfd_hbm_fill_pattern", "gfd_hbm_pattern_checksum", "gfd_hbm_scratch_bytes", "gfd_hbm_scratch_init", "gfd_hbm_read_checksum", "gfd_hbm_read_checksum_noalloc", "gfd_hbm_copy", "gfd_checksum_host",
     "gfd_probe_hbm", "gfd_probe_p2p", "gfd_probe_p2p_matrix", "gfd_cuda_device_by_uuid", "gfd_cuda_device_count",
 ]
 
@@ -112,6 +112,7 @@ _SIG = {
     "gfd_hbm_fill_pattern": (_int, [_vp, _sz, _u64, _vp]),
     "gfd_hbm_pattern_checksum": (_int, [_sz, _u64, _vp, _vp, _sz, _vp]),
     "gfd_hbm_scratch_bytes": (_sz, []),
+    "gfd_hbm_scratch_init": (_int, [_vp, _sz, _vp]),
     "gfd_hbm_read_checksum": (_int, [_vp, _sz, _vp, _vp, _sz, _vp]),
     "gfd_hbm_read_checksum_noalloc": (_int, [_vp, _sz, _vp, _vp]),
     "gfd_hbm_copy": (_int, [_vp, _vp, _sz, _vp]),
@@ -268,6 +269,10 @@ def vgpu_parse(config, cap=None):
 # ---- probes (device pointers are plain ints, e.g. torch.Tensor.data_ptr(); streams torch's .cuda_stream) ----
 def hbm_scratch_bytes():
     return int(lib.gfd_hbm_scratch_bytes())
+
+
+def hbm_scratch_init(d_scratch, scratch_bytes, stream=0):
+    _check(lib.gfd_hbm_scratch_init(d_scratch, scratch_bytes, stream), "gfd_hbm_scratch_init")
 
 
 def hbm_fill_pattern(d_buf, nbytes, seed=0, stream=0):

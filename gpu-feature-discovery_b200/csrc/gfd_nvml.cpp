@@ -278,6 +278,15 @@ int q_mig_profile_name(gfd_dev *m) {
     return fail(GFD_ERR_NO_MATCHING_PROFILE);
 }
 
+// Bench-only knob (bench.py --gpus N on a box with more than N GPUs): label only the first N device indices.  The CPU
+// baseline (oracle/ref_replay) honours the same variable the same way, so both arms label the same GPUs.  Unset in production.
+unsigned bench_device_cap(unsigned count) {
+    const char *e = getenv("GFD_B200_BENCH_MAX_DEVICES");
+    if (!e || !*e) return count;
+    long n = strtol(e, nullptr, 10);
+    return (n > 0 && (unsigned long)n < count) ? (unsigned)n : count;
+}
+
 int enumerate(gfd_mgr *m) {
     // devicelib.VisitDevices (device.go:206-236) incl. isSkipped (device.go:192-203)
     if (m->devices.done) return m->devices.rc;
@@ -285,6 +294,7 @@ int enumerate(gfd_mgr *m) {
     unsigned count = 0;
     int rc = NVCALL(m, DeviceGetCount, &count);
     if (rc) return m->devices.rc = rc;
+    count = bench_device_cap(count);
     for (unsigned i = 0; i < count; i++) {
         nvmlDevice_t h = nullptr;
         rc = NVCALL(m, DeviceGetHandleByIndex, i, &h);
@@ -510,6 +520,7 @@ GFD_API int gfd_prefetch(gfd_mgr *m, int threads) {
         // (device.go:206-236) would: the first failing index decides the error, skipped models are dropped.
         unsigned count = 0;
         int rc = NVCALL(m, DeviceGetCount, &count);
+        count = bench_device_cap(count);
         if (rc == 0 && count < 2) return 0;  // nothing to spread: leave the (serial) walk to gfd_device_count
         m->devices.done = true;
         if (rc) { m->devices.rc = rc; return 0; }  // reported by gfd_device_count, where the reference would see it

@@ -76,31 +76,93 @@ struct Fold {
     __device__ __forceinline__ void add(U2 v) { add(v.a); add(v.b); }
 };
 
-__device__ __forceinline__ void block_reduce_store(Fold f, ulonglong2 *partials) {
+// Scratch header (16 bytes, in front of the per-CTA partials).  BOTH words are zero whenever no launch is in flight: the
+// scratch is zeroed once when it is created (gfd_hbm_scratch_init; the no-alloc array by its static initialiser) and the
+// last CTA of every launch puts the zeros back, so a checksum is ONE kernel launch -- no memset, no finishing kernel.
+struct ScratchHeader {
+    unsigned long long tile_counter;  // next 64 KiB tile to hand out (hbm_read_fold_kernel)
+    unsigned int done;                // CTAs that have published their partial
+    unsigned int pad;
+};
+static_assert(sizeof(ScratchHeader) == 16, "header is one 16-byte slot");
+
+// CTA-wide fold of `f`; the result is valid in thread 0 only.
+__device__ __forceinline__ Fold block_fold(Fold f) {
     for (int o = 16; o > 0; o >>= 1) {
         f.x ^= __shfl_xor_sync(0xffffffffu, f.x, o);
         f.s += __shfl_xor_sync(0xffffffffu, f.s, o);
     }
     __shared__ uint64_t sx[kThreads / 32], ss[kThreads / 32];
-    int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    __syncthreads();  // the arrays may still be read by a previous block_fold of this CTA
     if (lane == 0) { sx[warp] = f.x; ss[warp] = f.s; }
     __syncthreads();
+    Fold r;
     if (warp == 0) {
-        uint64_t x = lane < kThreads / 32 ? sx[lane] : 0, s = lane < kThreads / 32 ? ss[lane] : 0;
+        r.x = lane < kThreads / 32 ? sx[lane] : 0;
+        r.s = lane < kThreads / 32 ? ss[lane] : 0;
         for (int o = 16; o > 0; o >>= 1) {
-            x ^= __shfl_xor_sync(0xffffffffu, x, o);
-            s += __shfl_xor_sync(0xffffffffu, s, o);
+            r.x ^= __shfl_xor_sync(0xffffffffu, r.x, o);
+            r.s += __shfl_xor_sync(0xffffffffu, r.s, o);
         }
-        if (lane == 0) partials[blockIdx.x] = make_ulonglong2(x, s);
+    }
+    return r;
+}
+
+// The < 16 tail bytes as (up to) two zero-padded little-endian 64-bit words.
+__device__ __forceinline__ Fold fold_tail(const unsigned char *__restrict__ tail, int tail_bytes) {
+    Fold f;
+    if (tail_bytes > 0) {
+        uint64_t w0 = 0, w1 = 0;
+        for (int b = 0; b < tail_bytes; b++) {
+            const uint64_t v = (uint64_t)tail[b] << (8 * (b & 7));
+            if (b < 8) w0 |= v; else w1 |= v;
+        }
+        f.add(w0);
+        if (tail_bytes > 8) f.add(w1);
+    }
+    return f;
+}
+
+// Publish this CTA's partial; the CTA that publishes LAST folds all of them, thread 0's `extra` and the `tail_bytes` (< 16)
+// bytes at `tail` into *out and re-arms the header for the next launch.  Classic last-block reduction: partial store ->
+// __threadfence -> ticket.
+__device__ __forceinline__ void publish_and_finish(Fold f, ScratchHeader *hdr, ulonglong2 *partials, Fold extra,
+                                                   const unsigned char *__restrict__ tail, int tail_bytes,
+                                                   gfd_checksum *__restrict__ out) {
+    Fold mine = block_fold(f);
+    __shared__ bool is_last;
+    if (threadIdx.x == 0) {
+        partials[blockIdx.x] = make_ulonglong2(mine.x, mine.s);
+        __threadfence();                                   // the partial is visible device-wide before the ticket is
+        const unsigned ticket = atomicAdd(&hdr->done, 1u);
+        is_last = (ticket == gridDim.x - 1);
+        if (is_last) __threadfence();                      // and every other CTA's partial is visible to us after it
+    }
+    __syncthreads();
+    if (!is_last) return;
+    Fold g;
+    for (unsigned i = threadIdx.x; i < gridDim.x; i += blockDim.x) {
+        const ulonglong2 p = __ldcg(&partials[i]);         // L2 is the point of coherence; never a stale L1 line
+        g.x ^= p.x;
+        g.s += p.y;
+    }
+    g = block_fold(g);
+    if (threadIdx.x == 0) {
+        const Fold t = fold_tail(tail, tail_bytes);
+        out->xor64 = g.x ^ extra.x ^ t.x;
+        out->sum64 = g.s + extra.s + t.s;
+        hdr->tile_counter = 0ull;                          // every CTA has drawn its last tile before taking a ticket
+        hdr->done = 0u;
     }
 }
 
-// n16 = number of whole 16-byte vectors; the < 16 tail bytes are folded by the finishing kernel.
-// `tile_counter` must be 0 at launch (the host side clears it on the same stream before every launch).
+// n16 = number of whole 16-byte vectors; `tail_bytes` (< 16) follow them.  hdr must be all-zero at launch (it is, unless a
+// launch sharing the scratch is still running) and is all-zero again when the kernel ends.
 template <bool kLocal>
 __global__ void __launch_bounds__(kThreads, kBlocksPerSM)
-hbm_read_fold_kernel(const char *__restrict__ src, size_t n16, unsigned long long *__restrict__ tile_counter,
-                     ulonglong2 *__restrict__ partials) {
+hbm_read_fold_kernel(const char *__restrict__ src, size_t n16, int tail_bytes, ScratchHeader *__restrict__ hdr,
+                     ulonglong2 *__restrict__ partials, gfd_checksum *__restrict__ out) {
     constexpr size_t kTile = (size_t)kThreads * kUnroll;  // 16-byte vectors per tile (64 KiB)
     const size_t full_tiles = n16 / kTile;
     Fold f;
@@ -108,12 +170,12 @@ hbm_read_fold_kernel(const char *__restrict__ src, size_t n16, unsigned long lon
     // Dynamic tile scheduler: thread 0 draws the NEXT tile index while the CTA streams the current one, so the
     // atomic's round trip hides behind 64 KiB of loads; the two-slot mailbox costs one barrier per tile.
     __shared__ unsigned long long next_tile[2];
-    if (threadIdx.x == 0) next_tile[0] = atomicAdd(tile_counter, 1ull);
+    if (threadIdx.x == 0) next_tile[0] = atomicAdd(&hdr->tile_counter, 1ull);
     __syncthreads();
     for (int slot = 0;; slot ^= 1) {
         const unsigned long long t = next_tile[slot];
         if (t >= full_tiles) break;
-        if (threadIdx.x == 0) next_tile[slot ^ 1] = atomicAdd(tile_counter, 1ull);
+        if (threadIdx.x == 0) next_tile[slot ^ 1] = atomicAdd(&hdr->tile_counter, 1ull);
         const char *base = src + (size_t)t * kTile * 16;
         U2 v[kUnroll];
 #pragma unroll
@@ -126,39 +188,7 @@ hbm_read_fold_kernel(const char *__restrict__ src, size_t n16, unsigned long lon
     for (size_t i = full_tiles * kTile + (size_t)blockIdx.x * kThreads + threadIdx.x; i < n16;
          i += (size_t)gridDim.x * kThreads)
         f.add(ld_stream16<kLocal>(src + i * 16, pol));
-    block_reduce_store(f, partials);
-}
-
-// One CTA: fold the per-block partials and the < 16 tail bytes (zero-padded to 64-bit words) into *out.
-__global__ void __launch_bounds__(256) fold_finish_kernel(const ulonglong2 *__restrict__ partials, int n_partials,
-                                                          const unsigned char *__restrict__ tail, int tail_bytes,
-                                                          gfd_checksum *__restrict__ out) {
-    uint64_t x = 0, s = 0;
-    for (int i = threadIdx.x; i < n_partials; i += blockDim.x) {
-        ulonglong2 p = partials[i];
-        x ^= p.x;
-        s += p.y;
-    }
-    if (threadIdx.x == 0 && tail_bytes > 0) {
-        uint64_t w[2] = {0, 0};
-        for (int b = 0; b < tail_bytes; b++) w[b >> 3] |= (uint64_t)tail[b] << (8 * (b & 7));
-        x ^= w[0]; s += w[0];
-        if (tail_bytes > 8) { x ^= w[1]; s += w[1]; }
-    }
-    for (int o = 16; o > 0; o >>= 1) {
-        x ^= __shfl_xor_sync(0xffffffffu, x, o);
-        s += __shfl_xor_sync(0xffffffffu, s, o);
-    }
-    __shared__ uint64_t sx[8], ss[8];
-    int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    if (lane == 0) { sx[warp] = x; ss[warp] = s; }
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        uint64_t X = 0, S = 0;
-        for (int i = 0; i < 8; i++) { X ^= sx[i]; S += ss[i]; }
-        out->xor64 = X;
-        out->sum64 = S;
-    }
+    publish_and_finish(f, hdr, partials, Fold(), reinterpret_cast<const unsigned char *>(src) + n16 * 16, tail_bytes, out);
 }
 
 // One 32 KiB tile per CTA; the last CTA's tile may be partial; CTA 0 also moves the < 16 tail bytes.
@@ -207,19 +237,21 @@ fill_pattern_kernel(char *__restrict__ dst, size_t n16, int tail_bytes, uint64_t
 // Comparing it with what hbm_read_fold_kernel found in HBM (or behind NVLink) turns a bandwidth probe into a
 // write -> read verification of every byte it touched.
 __global__ void __launch_bounds__(kThreads, kBlocksPerSM)
-pattern_fold_kernel(size_t n16, int tail_bytes, uint64_t seed, ulonglong2 *__restrict__ partials) {
+pattern_fold_kernel(size_t n16, int tail_bytes, uint64_t seed, ScratchHeader *__restrict__ hdr, ulonglong2 *__restrict__ partials,
+                    gfd_checksum *__restrict__ out) {
     Fold f;
     for (size_t i = (size_t)blockIdx.x * kThreads + threadIdx.x; i < n16; i += (size_t)gridDim.x * kThreads) {
         f.add(kGolden * (2 * i + seed));
         f.add(kGolden * (2 * i + 1 + seed));
     }
-    if (blockIdx.x == 0 && threadIdx.x == 0 && tail_bytes > 0) {  // the ragged tail keeps the LOW bytes of its words
+    Fold tail;
+    if (threadIdx.x == 0 && tail_bytes > 0) {  // the ragged tail keeps the LOW bytes of its words
         const int first = tail_bytes < 8 ? tail_bytes : 8, second = tail_bytes - first;
         const uint64_t w0 = kGolden * (2 * n16 + seed), w1 = kGolden * (2 * n16 + 1 + seed);
-        f.add(first == 8 ? w0 : (w0 & ((1ull << (8 * first)) - 1)));
-        if (second > 0) f.add(w1 & ((1ull << (8 * second)) - 1));
+        tail.add(first == 8 ? w0 : (w0 & ((1ull << (8 * first)) - 1)));
+        if (second > 0) tail.add(w1 & ((1ull << (8 * second)) - 1));
     }
-    block_reduce_store(f, partials);
+    publish_and_finish(f, hdr, partials, tail, nullptr, 0, out);
 }
 
 // ---- host side --------------------------------------------------------------------------------------
@@ -281,7 +313,7 @@ int grid_for(int sms, size_t n16) {
     return (int)(want < cap ? want : cap);
 }
 
-// Scratch layout: [0,16) header whose first 8 bytes are the tile counter, then one ulonglong2 partial per CTA.
+// Scratch layout: [0,16) ScratchHeader, then one ulonglong2 partial per CTA.  One launch, nothing else on the stream.
 // src_is_peer: d_buf is another GPU's memory reached through a peer mapping (the NVLink probe)
 int launch_read(int dev, const void *d_buf, size_t bytes, gfd_checksum *d_out, void *d_scratch, cudaStream_t st,
                 int *grid_out, bool src_is_peer = false) {
@@ -291,13 +323,10 @@ int launch_read(int dev, const void *d_buf, size_t bytes, gfd_checksum *d_out, v
     size_t n16 = bytes / 16;
     int tail = (int)(bytes % 16);
     int grid = grid_for(di.sms, n16);
-    auto *counter = static_cast<unsigned long long *>(d_scratch);
-    auto *partials = reinterpret_cast<ulonglong2 *>(static_cast<char *>(d_scratch) + 16);
-    CUDA_TRY(cudaMemsetAsync(counter, 0, 16, st));  // the scratch keeps the previous launch's counter: clear it
-    if (src_is_peer) hbm_read_fold_kernel<false><<<grid, kThreads, 0, st>>>(static_cast<const char *>(d_buf), n16, counter, partials);
-    else hbm_read_fold_kernel<true><<<grid, kThreads, 0, st>>>(static_cast<const char *>(d_buf), n16, counter, partials);
-    CUDA_TRY(cudaGetLastError());
-    fold_finish_kernel<<<1, 256, 0, st>>>(partials, grid, static_cast<const unsigned char *>(d_buf) + n16 * 16, tail, d_out);
+    auto *hdr = static_cast<ScratchHeader *>(d_scratch);
+    auto *partials = reinterpret_cast<ulonglong2 *>(static_cast<char *>(d_scratch) + sizeof(ScratchHeader));
+    if (src_is_peer) hbm_read_fold_kernel<false><<<grid, kThreads, 0, st>>>(static_cast<const char *>(d_buf), n16, tail, hdr, partials, d_out);
+    else hbm_read_fold_kernel<true><<<grid, kThreads, 0, st>>>(static_cast<const char *>(d_buf), n16, tail, hdr, partials, d_out);
     CUDA_TRY(cudaGetLastError());
     if (grid_out) *grid_out = grid;
     return 0;
@@ -340,17 +369,38 @@ int launch_pattern(int dev, size_t bytes, uint64_t seed, gfd_checksum *d_out, vo
     size_t cap = (size_t)di.sms * kBlocksPerSM;
     if (cap > (size_t)kMaxBlocks) cap = kMaxBlocks;
     int grid = (int)(want < 1 ? 1 : (want < cap ? want : cap));
-    auto *partials = reinterpret_cast<ulonglong2 *>(static_cast<char *>(d_scratch) + 16);
-    pattern_fold_kernel<<<grid, kThreads, 0, st>>>(n16, (int)(bytes % 16), seed, partials);
+    auto *hdr = static_cast<ScratchHeader *>(d_scratch);
+    auto *partials = reinterpret_cast<ulonglong2 *>(static_cast<char *>(d_scratch) + sizeof(ScratchHeader));
+    pattern_fold_kernel<<<grid, kThreads, 0, st>>>(n16, (int)(bytes % 16), seed, hdr, partials, d_out);
     CUDA_TRY(cudaGetLastError());
-    fold_finish_kernel<<<1, 256, 0, st>>>(partials, grid, nullptr, 0, d_out);
-    CUDA_TRY(cudaGetLastError());
+    return 0;
+}
+
+// a scratch this library allocates itself: zero the header once, right after cudaMalloc
+int alloc_scratch(void **out) {
+    CUDA_TRY(cudaMalloc(out, sizeof(ScratchHeader) + sizeof(ulonglong2) * (size_t)kMaxBlocks));
+    CUDA_TRY(cudaMemset(*out, 0, sizeof(ScratchHeader)));
+    CUDA_TRY(cudaDeviceSynchronize());  // the users are non-blocking streams, which do not order after the memset's stream
     return 0;
 }
 
 }  // namespace
 
-GFD_API size_t gfd_hbm_scratch_bytes(void) { return 16 + sizeof(ulonglong2) * (size_t)kMaxBlocks; }
+GFD_API size_t gfd_hbm_scratch_bytes(void) { return sizeof(ScratchHeader) + sizeof(ulonglong2) * (size_t)kMaxBlocks; }
+
+GFD_API int gfd_hbm_scratch_init(void *d_scratch, size_t scratch_bytes, void *stream) {
+    int n, dev;
+    int rc = device_count_checked(&n);
+    if (rc) return rc;
+    if (!d_scratch) return GFD_ERR_BAD_ARGUMENT;
+    if (scratch_bytes < gfd_hbm_scratch_bytes()) return GFD_ERR_BUFFER_TOO_SMALL;
+    if ((uintptr_t)d_scratch % 16) return GFD_ERR_ALIGNMENT;
+    if ((rc = device_of_pointer(d_scratch, &dev))) return rc;
+    DeviceScope scope(dev);
+    if (scope.rc) return scope.rc;
+    CUDA_TRY(cudaMemsetAsync(d_scratch, 0, sizeof(ScratchHeader), static_cast<cudaStream_t>(stream)));
+    return 0;
+}
 
 GFD_API int gfd_cuda_device_count(int *count) {
     if (!count) return GFD_ERR_BAD_ARGUMENT;
@@ -435,15 +485,17 @@ GFD_API int gfd_hbm_copy(void *d_dst, const void *d_src, size_t bytes, void *str
 //   * the FIRST call on each GPU looks the array's device address up (cudaGetSymbolAddress), which may make the
 //     driver load this library's kernels on that GPU.  Make that first call early, before any stream capture;
 //   * all calls on one GPU share the one array and it keeps what the last call left there.  The only part that
-//     must start at zero is the 16-byte header (the tile counter the CTAs draw work from); every call clears it
-//     on the caller's stream before launching.  The partial-sum slots need no clearing: each launched CTA
-//     overwrites its own slot and the finishing kernel reads exactly the slots of that launch.  But two calls
-//     that run on the GPU at the same time (different streams, or different host threads) share the counter and
-//     the slots and corrupt each other's result: keep calls on one stream, or order them.
+//     must start at zero is the 16-byte header (the tile counter the CTAs draw work from and the count of CTAs
+//     that have finished).  It is zero when the library's device image is loaded (static initialiser), and the
+//     kernel itself puts the zeros back as its last act, so every call finds it cleared without any memset on
+//     the caller's stream.  The partial-sum slots need no clearing: each launched CTA overwrites its own slot
+//     and the last CTA reads exactly the slots of that launch.  But two calls that run on the GPU at the same
+//     time (different streams, or different host threads) share the counters and the slots and corrupt each
+//     other's result -- and can leave the header non-zero for later calls: keep calls on one stream, or order them.
 namespace {
 constexpr int kNoAllocMaxBlocks = 1024;
 constexpr size_t kNoAllocMaxBytes = 16ull << 30;
-static __device__ __align__(256) ulonglong2 g_noalloc_partials[kNoAllocMaxBlocks];
+static __device__ __align__(256) ulonglong2 g_noalloc_partials[kNoAllocMaxBlocks] = {};  // slot 0 = ScratchHeader, zero at load
 
 // In host code `g_noalloc_partials` is only a handle for the runtime, not an address a kernel can use.
 // The real per-device address is resolved once per GPU, with that GPU current, and cached here.
@@ -475,6 +527,8 @@ GFD_API int gfd_hbm_read_checksum_noalloc(const void *d_buf, size_t bytes, gfd_c
     if (bytes > kNoAllocMaxBytes) return GFD_ERR_SIZE_LIMIT;
     if ((uintptr_t)d_buf % 16 || (uintptr_t)d_out % 8) return GFD_ERR_ALIGNMENT;
     if ((rc = device_of_pointer(d_out, &dev))) return rc;
+    int src_dev = dev;
+    if (bytes && (rc = device_of_pointer(d_buf, &src_dev))) return rc;  // a host or stale pointer is refused here, not faulted on
     DeviceScope scope(dev);
     if (scope.rc) return scope.rc;
     DevInfo di;
@@ -482,7 +536,7 @@ GFD_API int gfd_hbm_read_checksum_noalloc(const void *d_buf, size_t bytes, gfd_c
     if (grid_for(di.sms, bytes / 16) > kNoAllocMaxBlocks - 1) return GFD_ERR_SIZE_LIMIT;  // slot 0 is the header
     void *scratch = nullptr;
     if ((rc = noalloc_scratch(dev, &scratch))) return rc;
-    return launch_read(dev, d_buf, bytes, d_out, scratch, static_cast<cudaStream_t>(stream), nullptr);
+    return launch_read(dev, d_buf, bytes, d_out, scratch, static_cast<cudaStream_t>(stream), nullptr, src_dev != dev);
 }
 
 // ---- host-buffer form ---------------------------------------------------------------------------------
@@ -511,7 +565,7 @@ GFD_API int gfd_checksum_host(int cuda_device, const void *host_buf, size_t byte
     Staging &s = g_staging[cuda_device];
     // each piece is created on its own so that a call that failed half-way (out of memory) is completed by the next one
     if (!s.st) CUDA_TRY(cudaStreamCreateWithFlags(&s.st, cudaStreamNonBlocking));
-    if (!s.d_scratch) CUDA_TRY(cudaMalloc(&s.d_scratch, gfd_hbm_scratch_bytes()));
+    if (!s.d_scratch && (rc = alloc_scratch(&s.d_scratch))) return rc;
     if (!s.d_out) CUDA_TRY(cudaMalloc((void **)&s.d_out, sizeof(gfd_checksum)));
     size_t need = (bytes + 255) / 256 * 256;
     if (need > s.cap) {
@@ -557,7 +611,7 @@ int time_kernel(int run_dev, void *dst, const void *src, size_t bytes, int warmu
     Stream st;
     CUDA_TRY(cudaStreamCreateWithFlags(&st.s, cudaStreamNonBlocking));
     Buf scratch, d_out;
-    CUDA_TRY(cudaMalloc(&scratch.p, gfd_hbm_scratch_bytes()));
+    if ((rc = alloc_scratch(&scratch.p))) return rc;
     CUDA_TRY(cudaMalloc(&d_out.p, sizeof(gfd_checksum)));
     Ev e0, e1;
     CUDA_TRY(cudaEventCreate(&e0.e));
@@ -750,7 +804,7 @@ GFD_API int gfd_probe_p2p_matrix(int n_devices, size_t bytes, int warmup, int it
             }
             CUDA_TRY(cudaMalloc(&dev[d].src, bytes));
             if (mode != GFD_PROBE_READ) CUDA_TRY(cudaMalloc(&dev[d].dst, bytes));
-            CUDA_TRY(cudaMalloc(&dev[d].scratch, gfd_hbm_scratch_bytes()));
+            { int arc = alloc_scratch(&dev[d].scratch); if (arc) return arc; }
             CUDA_TRY(cudaMalloc(&dev[d].out, sizeof(gfd_checksum)));
             CUDA_TRY(cudaStreamCreateWithFlags(&dev[d].st, cudaStreamNonBlocking));
             CUDA_TRY(cudaEventCreate(&dev[d].e0));

@@ -215,17 +215,24 @@ typedef struct gfd_checksum {
 int gfd_hbm_fill_pattern(void *d_buf, size_t bytes, uint64_t seed, void *stream);
 
 /* The checksum a buffer of `bytes` filled by gfd_hbm_fill_pattern(…, seed) must have, computed on the GPU from the
- * pattern's definition without reading any buffer (same scratch rules as gfd_hbm_read_checksum; the device is the one
- * d_out lives on).  fill -> read_checksum == pattern_checksum is a write/read verification of the memory in between;
+ * pattern's definition without reading any buffer (same scratch rules as gfd_hbm_read_checksum -- header zeroed once with
+ * gfd_hbm_scratch_init, declared below; the device is the one d_out lives on).  fill -> read_checksum == pattern_checksum is a write/read verification of the memory in between;
  * the self-contained probes below do exactly that and fail with GFD_ERR_DATA_MISMATCH otherwise. */
 int gfd_hbm_pattern_checksum(size_t bytes, uint64_t seed, gfd_checksum *d_out, void *d_scratch, size_t scratch_bytes,
                              void *stream);
 /* Bytes of device scratch gfd_hbm_read_checksum needs, for any input size: a 16-byte header (the tile counter the
- * CTAs draw work from; the call clears it on `stream` before launching) + one 16-byte partial sum per CTA.  The
- * scratch needs no initialisation by the caller, but two calls sharing one scratch must not overlap on the GPU. */
+ * CTAs draw work from + the count of finished CTAs) + one 16-byte partial sum per CTA.
+ * The header must be ZERO before the first call that uses a scratch: call gfd_hbm_scratch_init() once after allocating it
+ * (or zero its first 16 bytes yourself).  After that nothing is cleared per call: a checksum is exactly one kernel launch,
+ * whose last CTA folds the partials, writes the result and puts the header back to zero.  Two calls sharing one scratch
+ * must not overlap on the GPU (they would share the counters, and could leave them non-zero: re-init the scratch then). */
 size_t gfd_hbm_scratch_bytes(void);
+/* Zero the scratch header on `stream` (asynchronous).  Once per scratch allocation; also the way to recover a scratch
+ * whose last user was killed mid-launch or raced with another. */
+int gfd_hbm_scratch_init(void *d_scratch, size_t scratch_bytes, void *stream);
 /* hbm_read_probe: stream `bytes` from HBM with 128-bit coalesced loads and fold them into *d_out
- * (device memory).  Algorithmic traffic: `bytes` read.  d_scratch: gfd_hbm_scratch_bytes() bytes. */
+ * (device memory).  Algorithmic traffic: `bytes` read.  d_scratch: gfd_hbm_scratch_bytes() bytes, initialised once
+ * (above).  One kernel launch on `stream`, nothing else. */
 int gfd_hbm_read_checksum(const void *d_buf, size_t bytes, gfd_checksum *d_out, void *d_scratch,
                           size_t scratch_bytes, void *stream);
 /* Copy variant: d_dst[i] = d_src[i].  Algorithmic traffic: 2 * bytes.  Either pointer may be a
@@ -238,12 +245,16 @@ int gfd_hbm_copy(void *d_dst, const void *d_src, size_t bytes, void *stream);
  * or tip the job over), code living under a framework's allocator rules.  The per-CTA partial sums go to a fixed
  * 16 KiB array inside the library's device image (each GPU that loads the library's kernels holds it until exit).
  *   - bytes <= GFD_NOALLOC_MAX_BYTES, else GFD_ERR_SIZE_LIMIT (split the buffer at 8-byte multiples and combine
- *     the pieces: xor of xor64, sum of sum64); also GFD_ERR_SIZE_LIMIT on a GPU needing more than 1024 CTAs.
+ *     the pieces: xor of xor64, sum of sum64); also GFD_ERR_SIZE_LIMIT on a GPU whose launch would need more than
+ *     1023 CTAs (the array holds a 16-byte header + 1023 partials; a B200 uses 296).
  *   - the first call on each GPU resolves the array's address and may load the kernels there: do it once at
  *     start-up, before any stream capture begins.
- *   - calls on the same GPU share the array; ones that overlap in time on the GPU corrupt each other.  Issue them
- *     on one stream or serialise them.  Nothing needs clearing between calls.
- * Same result, bit for bit, as gfd_hbm_read_checksum.  d_buf 16-byte aligned, d_out device memory. */
+ *   - calls on the same GPU share the array; ones that overlap in time on the GPU corrupt each other (and may leave
+ *     the header non-zero, which spoils later calls too).  Issue them on one stream or serialise them.  Nothing needs
+ *     clearing between calls: the header is zero when the library is loaded and each launch zeroes it again as it ends.
+ *   - d_buf is checked like gfd_hbm_read_checksum's: it must be device (or managed) memory, on the GPU of d_out or on a
+ *     peer that GPU has mapped; a host pointer is refused with GFD_ERR_BAD_ARGUMENT instead of faulting the context.
+ * Same result, bit for bit, as gfd_hbm_read_checksum.  d_buf 16-byte aligned, d_out device memory.  One kernel launch. */
 #define GFD_NOALLOC_MAX_BYTES (16ull << 30)
 int gfd_hbm_read_checksum_noalloc(const void *d_buf, size_t bytes, gfd_checksum *d_out, void *stream);
 

@@ -16,7 +16,7 @@
  * call and (b) its label file equals the oracle's, on every fixture.
  *
  *   ref_replay [--mig-strategy S] [--no-timestamp] [--machine-type-file F] [-o OUT] [--passes N] [--pci-root DIR]
- * prints one JSON line: {"passes":N,"ms":[...],"init_ms":[...],"nvml_calls":C,"dl_cycles":D,"ok":true}
+ * prints one JSON line: {"passes":N,"ms":[...],"init_ms":[...],"shutdown_ms":[...],"nvml_calls":C,"dl_cycles":D,"ok":true}
  *
  * Map-order caveat: the reference ranges over Go maps; like the product and the oracle this uses sorted order.
  * Not restated here: config file / time-slicing (replicas are always 1 / 0) and the vGPU sysfs scan beyond
@@ -85,8 +85,11 @@ static int ref_init(void) {
     return rc;
 }
 
+static double g_shutdown_ms;
 static void ref_shutdown(void) {
+    double t0 = now_ms();
     if (NV(nvmlReturn_t, "nvmlShutdown", void)() == NVML_SUCCESS) dlclose(g_lib);
+    g_shutdown_ms = now_ms() - t0;
 }
 
 /* nvmlLookupSymbol (device.go:326-338): a full dlopen/dlsym/dlclose cycle per call */
@@ -136,6 +139,11 @@ static int get_devices(nvmlDevice_t *out, int *n) {
     unsigned count = 0;
     int rc = NV(nvmlReturn_t, "nvmlDeviceGetCount_v2", unsigned *)(&count);
     if (rc) return rc;
+    {   /* bench-only: bench.py --gpus N labels the first N indices in BOTH arms (same variable as the product's shim) */
+        const char *cap = getenv("GFD_B200_BENCH_MAX_DEVICES");
+        long c = cap && *cap ? strtol(cap, NULL, 10) : 0;
+        if (c > 0 && (unsigned long)c < count) count = (unsigned)c;
+    }
     *n = 0;
     for (unsigned i = 0; i < count; i++) {
         nvmlDevice_t h;
@@ -659,7 +667,7 @@ int main(int argc, char **argv) {
         else if (!strcmp(argv[i], "--no-timestamp")) no_ts = 1;
         else { fprintf(stderr, "ref_replay: unknown argument %s\n", argv[i]); return 2; }
     }
-    double *ms = calloc((size_t)passes, sizeof(double)), *init = calloc((size_t)passes, sizeof(double));
+    double *ms = calloc((size_t)passes, sizeof(double)), *init = calloc((size_t)passes, sizeof(double)), *shut = calloc((size_t)passes, sizeof(double));
     long long ts = (long long)time(NULL);  /* NewTimestampLabeler: once per run() */
     unsigned long calls_per_pass = 0, dl_per_pass = 0;
     for (int p = 0; p < passes; p++) {
@@ -675,6 +683,7 @@ int main(int argc, char **argv) {
         if (write_file(&labels, out)) return 1;
         ms[p] = now_ms() - t0;
         init[p] = g_init_ms;
+        shut[p] = g_shutdown_ms;
         calls_per_pass = g_calls;
         dl_per_pass = g_dl;
         free(labels.e); free(nv.e); free(vg.e);
@@ -684,6 +693,8 @@ int main(int argc, char **argv) {
     for (int p = 0; p < passes; p++) fprintf(js, "%s%.4f", p ? "," : "", ms[p]);
     fprintf(js, "],\"init_ms\":[");
     for (int p = 0; p < passes; p++) fprintf(js, "%s%.4f", p ? "," : "", init[p]);
+    fprintf(js, "],\"shutdown_ms\":[");
+    for (int p = 0; p < passes; p++) fprintf(js, "%s%.4f", p ? "," : "", shut[p]);
     fprintf(js, "],\"nvml_calls\":%lu,\"dl_cycles\":%lu,\"ok\":true}\n", calls_per_pass, dl_per_pass);
     return 0;
 }

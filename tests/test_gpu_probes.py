@@ -26,7 +26,10 @@ def env():
     orc.oracle_fill_pattern.argtypes = [ctypes.c_void_p, ctypes.c_size_t, ctypes.c_uint64]
     orc.oracle_pattern_checksum.argtypes = [ctypes.c_size_t, ctypes.c_uint64, ctypes.POINTER(ctypes.c_uint64)]
     dev = torch.device("cuda:0")
-    scratch = torch.empty(B.hbm_scratch_bytes(), dtype=torch.uint8, device=dev)
+    # garbage on purpose: the one-time gfd_hbm_scratch_init is what makes the header usable, nothing is cleared per call
+    scratch = torch.full((B.hbm_scratch_bytes(),), 0xA5, dtype=torch.uint8, device=dev)
+    B.hbm_scratch_init(scratch.data_ptr(), scratch.numel(), torch.cuda.current_stream().cuda_stream)
+    torch.cuda.synchronize()
     out = torch.zeros(2, dtype=torch.int64, device=dev)
 
     class Env:

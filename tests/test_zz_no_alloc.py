@@ -8,7 +8,9 @@ call's partial sums, so the second call is the one that would expose stale-scrat
 
 This file sorts last on purpose: if it fails under `pytest -x`, everything else has already run.  It does not
 depend on state left by other tests and passes in a fresh process on its own."""
+import ctypes
 import importlib
+import os
 
 import numpy as np
 import pytest
@@ -28,9 +30,21 @@ def ctx():
     c = Ctx()
     c.torch, c.B, c.dev = torch, B, dev
     c.scratch = torch.empty(B.hbm_scratch_bytes(), dtype=torch.uint8, device=dev)
+    B.hbm_scratch_init(c.scratch.data_ptr(), c.scratch.numel(), torch.cuda.current_stream().cuda_stream)  # the allocating sibling's one-time set-up
     c.out_ref = torch.zeros(2, dtype=torch.int64, device=dev)
     c.out_new = torch.zeros(2, dtype=torch.int64, device=dev)
+    # the CPU statement of the checksum (test infrastructure): the no-alloc path is also held against it directly
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    c.orc = ctypes.CDLL(os.path.join(root, "oracle", "libgfd_oracle_c.so"))
+    c.orc.oracle_checksum.argtypes = [ctypes.c_void_p, ctypes.c_size_t, ctypes.POINTER(ctypes.c_uint64)]
     return c
+
+
+def oracle_entry_point(c, host):
+    o = (ctypes.c_uint64 * 2)()
+    host = np.ascontiguousarray(host, dtype=np.uint8)
+    c.orc.oracle_checksum(host.ctypes.data, host.size, o)
+    return int(o[0]), int(o[1])
 
 
 def reference_entry_point(c, t, n):
@@ -100,3 +114,72 @@ def test_bad_pointers_are_refused(ctx):
     with pytest.raises(B.GfdError) as ei:
         B.hbm_read_checksum_noalloc(t.data_ptr(), 256, 0, 0)
     assert ei.value.status == B.GFD_ERR_BAD_ARGUMENT
+
+
+@pytest.mark.parametrize("n", [0, 1, 15, 16, 65536 + 3, (48 << 20) + 11])
+def test_matches_the_cpu_oracle_directly_twice(ctx, n):
+    """Not only equal to the other GPU entry point: equal to the byte-at-a-time C statement of the checksum, on random bytes,
+    on two calls in a row (the second call meets the array as the first one left it)."""
+    host = np.random.default_rng(31337 + n).integers(0, 256, size=n, dtype=np.uint8)
+    t = ctx.torch.from_numpy(host).to(ctx.dev) if n else ctx.torch.empty(0, dtype=ctx.torch.uint8, device=ctx.dev)
+    want = oracle_entry_point(ctx, host)
+    assert noalloc_entry_point(ctx, t, n) == want
+    assert noalloc_entry_point(ctx, t, n) == want
+
+
+def test_host_pointer_is_refused_not_faulted(ctx):
+    """A pageable host address as the input must come back as BAD_ARGUMENT (or the runtime's invalid-value code), exactly as
+    the allocating entry point answers -- not as an illegal-address fault that kills the caller's CUDA context.  The GPU must
+    still work afterwards."""
+    B = ctx.B
+    host = np.zeros(4096 + 16, dtype=np.uint8)
+    addr = (host.ctypes.data + 15) // 16 * 16
+    st_new = B.lib.gfd_hbm_read_checksum_noalloc(addr, 4096, ctx.out_new.data_ptr(), 0)
+    st_ref = B.lib.gfd_hbm_read_checksum(addr, 4096, ctx.out_ref.data_ptr(), ctx.scratch.data_ptr(), ctx.scratch.numel(), 0)
+    assert st_new != 0 and st_new == st_ref
+    assert st_new in (B.GFD_ERR_BAD_ARGUMENT, 100000 + 1)
+    ctx.torch.cuda.synchronize()                    # no sticky error
+    t = device_bytes(ctx, 70001, 5)
+    assert noalloc_entry_point(ctx, t, 70001) == reference_entry_point(ctx, t, 70001)
+
+
+def test_second_gpu_gets_its_own_array_address(ctx):
+    """The array's device address differs per GPU and is looked up on first use per GPU: call on cuda:0 first, then cuda:1,
+    then cuda:0 again, each twice, each against the allocating entry point on the same GPU."""
+    torch, B = ctx.torch, ctx.B
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    n = (8 << 20) + 40
+    host = np.random.default_rng(99).integers(0, 256, size=n, dtype=np.uint8)
+    want = oracle_entry_point(ctx, host)
+    for dev_index in (0, 1, 0, 1):
+        dev = torch.device("cuda:%d" % dev_index)
+        with torch.cuda.device(dev):
+            t = torch.from_numpy(host).to(dev)
+            out = torch.zeros(2, dtype=torch.int64, device=dev)
+            scratch = torch.zeros(B.hbm_scratch_bytes(), dtype=torch.uint8, device=dev)
+            st = torch.cuda.current_stream(dev)
+            for _ in range(2):
+                out.fill_(-1)
+                B.hbm_read_checksum_noalloc(t.data_ptr(), n, out.data_ptr(), st.cuda_stream)
+                st.synchronize()
+                assert tuple(int(v) for v in out.cpu().numpy().view(np.uint64)) == want
+            out.fill_(-1)
+            B.hbm_read_checksum(t.data_ptr(), n, out.data_ptr(), scratch.data_ptr(), scratch.numel(), st.cuda_stream)
+            st.synchronize()
+            assert tuple(int(v) for v in out.cpu().numpy().view(np.uint64)) == want
+
+
+def test_peer_source_is_read_through_the_mapping(ctx):
+    """Input on cuda:1, result on cuda:0: the kernel runs on cuda:0 and pulls the bytes over NVLink (needs 2 GPUs with
+    peer access, which torch enables on the first cross-device copy)."""
+    torch, B = ctx.torch, ctx.B
+    if torch.cuda.device_count() < 2 or not torch.cuda.can_device_access_peer(0, 1):
+        pytest.skip("needs 2 peer-capable GPUs")
+    n = (4 << 20) + 24
+    host = np.random.default_rng(123).integers(0, 256, size=n, dtype=np.uint8)
+    far = torch.from_numpy(host).to("cuda:1")
+    near = far.to("cuda:0")                         # makes torch enable peer access 0 <-> 1
+    torch.cuda.synchronize()
+    assert noalloc_entry_point(ctx, far, n) == oracle_entry_point(ctx, host)
+    assert noalloc_entry_point(ctx, near, n) == oracle_entry_point(ctx, host)

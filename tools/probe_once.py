@@ -7,7 +7,7 @@ n = int(sys.argv[1]) if len(sys.argv) > 1 else (4 << 30)
 dev = torch.device("cuda:0")
 buf = torch.empty(n, dtype=torch.uint8, device=dev)
 dst = torch.empty(n, dtype=torch.uint8, device=dev)
-scratch = torch.empty(B.hbm_scratch_bytes(), dtype=torch.uint8, device=dev)
+scratch = torch.zeros(B.hbm_scratch_bytes(), dtype=torch.uint8, device=dev)  # header must start at zero (gfd_hbm_scratch_init)
 out = torch.zeros(2, dtype=torch.int64, device=dev)
 st = torch.cuda.current_stream().cuda_stream
 B.hbm_fill_pattern(buf.data_ptr(), n, 0, st)
