@@ -9,7 +9,8 @@ node, MIG strategy none, --no-timestamp, full label set from the real NVML, vGPU
 file write).  The reference has no GPU compute on this path, so:
 
   metric / value   labeling_pass_ms: steady-state wall-clock of one pass inside the running labeler
-                   (gpu-feature-discovery --passes K+W --sleep-interval 0s --timing; mean of the last K).
+                   (gpu-feature-discovery --passes N --sleep-interval 0s --timing): W untimed warm-up passes, then exactly K
+                   timed ones; `value` = their MEDIAN (single passes on a shared host jump to 30-400 ms), `ms_per_step` = mean.
   e2e              the same work as a user gets it: exec -> exit of `gpu-feature-discovery --oneshot
                    --no-timestamp -o FILE` plus reading FILE back (median over the K runs; the mean is kept beside
                    it: process spawns on a shared host have 40-270 ms outliers).  The path moves no tensor data, so
@@ -20,13 +21,18 @@ file write).  The reference has no GPU compute on this path, so:
   roofline         the dominant (only) GPU kernel, hbm_read_fold, 4 GiB per launch (>> 126 MB L2: no flush
                    needed), timed live with CUDA events on the launching stream; algorithmic bytes = buffer size.
   cpu_baseline     oracle/ref_replay: a call-sequence-faithful C replay of the reference's pass (the Go reference
-                   cannot be built on this image), single-threaded like the reference.  kind = "port".
+                   cannot be built on this image), single-threaded like the reference.  kind = "port".  Its passes are
+                   INTERLEAVED with the product's (chunks of 5, A B A B ...) so both see the same GPU / driver state.
+  roofline_p2p     N >= 2: the NVLink probe kernels (peer-mapped loads = READ, peer stores = PUSH) over all directed pairs
+                   of the N GPUs, concurrent tournament schedule, every transfer verified against the pattern's checksum.
 
 `--impl reference` times that replay alone (rank 0 only under torchrun) and prints the same line shape.
-N > 1: the pass is per node and does not shard across ranks, so rank 0 runs it once over all N GPUs (the labeler's own
-per-GPU host threads are the multi-GPU path) while every rank probes its own GPU (replicas); probe GB/s is the sum.
-Barriers between the regions go over a gloo group: a rank waiting in an NCCL barrier spins a kernel on its GPU, which
-is one of the GPUs rank 0's pass is attaching to.
+N > 1: the pass is per node and does not shard across ranks, so rank 0 runs it once over the first N GPUs (the labeler's own
+per-GPU host threads are the multi-GPU path; GFD_B200_BENCH_MAX_DEVICES=N caps BOTH arms' enumeration, NVML ignores
+CUDA_VISIBLE_DEVICES) while every rank probes its own GPU (replicas); probe GB/s is the sum.  NO rank creates a CUDA context
+before the labeling passes and the one-shot runs are over: the process group starts on gloo (host-side barriers), CUDA and
+the NCCL group (result reduction only -- the data path has no collective) come up afterwards.  So the node is in the same
+state as under `--impl reference`, whose other ranks exit at once.
 """
 import argparse
 import ctypes
@@ -96,112 +102,101 @@ class ClockSampler(threading.Thread):
         return {"sm_mhz": statistics.median(sm), "sm_max_mhz": max(mx), "reasons": sorted(reasons), "samples": len(sm)}
 
 
-PHASES = {}  # filled by parse_timing: mean ms of the NVML bracket's phases over the steady-state passes of the last run
+CHUNK = 5  # timed passes per process in the interleaved series (each process adds one untimed pass of its own first)
+PHASE_KEYS = ("init", "attach", "labels", "shutdown")
+
+
+def bench_env(gpus):
+    """Both arms label the first `gpus` device indices (NVML itself always attaches every GPU the container shows)."""
+    return dict(os.environ, GFD_B200_BENCH_MAX_DEVICES=str(gpus))
 
 
 def parse_timing(stderr):
-    out, ph = [], []
+    """-> [(pass ms, {init, attach, labels, shutdown})] from the labeler's --timing lines."""
+    out = []
     for line in stderr.splitlines():
-        if "timing: pass " in line:
-            out.append(float(line.split("timing: pass ")[1].split(" ms")[0]))
-            if "[init " in line:
-                body = line.split("[init ")[1].rstrip("]")
-                vals = [float(x.split()[-1]) for x in ("init " + body).split(",")]
-                ph.append(vals)
-    if ph:
-        PHASES.clear()
-        PHASES.update({k: round(sum(v[i] for v in ph) / len(ph), 3) for i, k in enumerate(("init", "attach", "labels", "shutdown"))})
+        if "timing: pass " not in line:
+            continue
+        ms = float(line.split("timing: pass ")[1].split(" ms")[0])
+        ph = {}
+        if "[init " in line:
+            body = line.split("[init ")[1].rstrip("]")
+            vals = [float(x.split()[-1]) for x in ("init " + body).split(",")]
+            ph = dict(zip(PHASE_KEYS, vals))
+        out.append((ms, ph))
     return out
 
 
-def product_passes(binary, passes, out_file, extra=()):
+def product_passes(binary, passes, out_file, env, extra=()):
     p = subprocess.run([binary, "--passes", str(passes), "--sleep-interval", "0s", "--timing", "--no-timestamp", "--mig-strategy=none",
-                        "-o", out_file] + list(extra), capture_output=True, text=True, timeout=600)
+                        "-o", out_file] + list(extra), capture_output=True, text=True, timeout=600, env=env)
     if p.returncode != 0:
         raise RuntimeError("gpu-feature-discovery failed:\n" + p.stderr[-2000:])
-    ms = parse_timing(p.stderr)
-    if len(ms) != passes:
-        raise RuntimeError("expected %d timing lines, got %d" % (passes, len(ms)))
-    return ms
+    rows = parse_timing(p.stderr)
+    if len(rows) != passes:
+        raise RuntimeError("expected %d timing lines, got %d" % (passes, len(rows)))
+    return rows
 
 
-def product_oneshot(binary, out_file):
+def replay_passes(passes, out_file, env):
+    """-> (rows [(pass ms, {init, shutdown})], stats) from oracle/ref_replay's JSON line."""
+    p = subprocess.run([REPLAY, "--mig-strategy", "none", "--no-timestamp", "-o", out_file, "--passes", str(passes)],
+                       capture_output=True, text=True, timeout=600, env=env)
+    if p.returncode != 0:
+        raise RuntimeError("ref_replay failed:\n" + p.stderr[-2000:])
+    r = json.loads(p.stdout.strip().splitlines()[-1])
+    rows = [(ms, {"init": i, "shutdown": s}) for ms, i, s in zip(r["ms"], r["init_ms"], r.get("shutdown_ms", [0.0] * len(r["ms"])))]
+    return rows, r
+
+
+def oneshot(argv, out_file, env):
+    """exec -> exit of a one-shot run + reading the label file back: the user-facing call."""
     t0 = time.perf_counter()
-    p = subprocess.run([binary, "--oneshot", "--no-timestamp", "--mig-strategy=none", "-o", out_file], capture_output=True, timeout=120)
+    p = subprocess.run(argv, capture_output=True, timeout=120, env=env)
     with open(out_file, "rb") as f:
         data = f.read()
     dt = (time.perf_counter() - t0) * 1e3
     if p.returncode != 0:
-        raise RuntimeError("gpu-feature-discovery --oneshot failed:\n" + p.stderr.decode()[-2000:])
+        raise RuntimeError("%s failed:\n%s" % (argv[0], p.stderr.decode()[-2000:]))
     return dt, data
 
 
-def replay_passes(passes, out_file):
-    p = subprocess.run([REPLAY, "--mig-strategy", "none", "--no-timestamp", "-o", out_file, "--passes", str(passes)],
-                       capture_output=True, text=True, timeout=600)
-    if p.returncode != 0:
-        raise RuntimeError("ref_replay failed:\n" + p.stderr[-2000:])
-    return json.loads(p.stdout.strip().splitlines()[-1])
+def product_oneshot_argv(binary, out_file):
+    return [binary, "--oneshot", "--no-timestamp", "--mig-strategy=none", "-o", out_file]
+
+
+def replay_oneshot_argv(out_file):
+    return [REPLAY, "--mig-strategy", "none", "--no-timestamp", "-o", out_file]
+
+
+def series(warmup, steps, run_a, run_b=None):
+    """W untimed warm-up passes, then exactly K timed ones, in chunks of CHUNK passes per process; every process runs one
+    extra pass first that is not a step (its dlopen and page-ins are process start-up, which `e2e` measures, not the
+    steady state).  With run_b the two implementations alternate chunk by chunk: A B A B ..."""
+    run_a(warmup)
+    if run_b:
+        run_b(warmup)
+    a, b, left = [], [], steps
+    while left > 0:
+        c = min(CHUNK, left)
+        a += run_a(1 + c)[1:]
+        if run_b:
+            b += run_b(1 + c)[1:]
+        left -= c
+    return a, b
+
+
+def stats(rows):
+    ms = [r[0] for r in rows]
+    keys = sorted({k for _, ph in rows for k in ph})
+    phases = {k: round(statistics.median([ph[k] for _, ph in rows if k in ph]), 4) for k in keys}
+    return {"median": round(statistics.median(ms), 4), "mean": round(sum(ms) / len(ms), 4), "min": round(min(ms), 4),
+            "max": round(max(ms), 4), "n": len(ms)}, phases
 
 
 def diff_lines(a, b):
     sa, sb = set(a.splitlines()), set(b.splitlines())
     return len(sa ^ sb)
-
-
-def reference_arm(args, rank, world):
-    if rank != 0:
-        return 0
-    tmp = tempfile.mkdtemp(prefix="gfd-bench-")
-    out = os.path.join(tmp, "gfd")
-    total = args.warmup + args.steps
-    r = replay_passes(total, out)
-    ms = r["ms"][args.warmup:]
-    value = sum(ms) / len(ms)
-    spread = {"median": round(statistics.median(ms), 4), "min": round(min(ms), 4), "max": round(max(ms), 4)}
-    e2e = []
-    for i in range(total):  # same definition as the product arm's e2e: exec -> exit of a one-shot run + reading the file
-        t0 = time.perf_counter()
-        p = subprocess.run([REPLAY, "--mig-strategy", "none", "--no-timestamp", "-o", out], capture_output=True, timeout=120)
-        with open(out, "rb") as f:
-            f.read()
-        if p.returncode != 0:
-            raise RuntimeError("ref_replay failed: " + p.stderr.decode()[-1000:])
-        if i >= args.warmup:
-            e2e.append((time.perf_counter() - t0) * 1e3)
-    e2e_ms = statistics.median(e2e)
-    line = {
-        "impl": "reference", "metric": "labeling_pass_ms", "value": round(value, 4), "unit": "ms", "n_gpus": args.gpus,
-        "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(value, 4), "higher_is_better": False, "scaling": "weak",
-        "vs_baseline": None, "dtype": "u64", "data": "real NVML of this host (no synthetic input: the pass reads the driver)",
-        "config": workload_config(),
-        "cpu_baseline": {"value": round(value, 4), "unit": "ms", "cores": 1, "kind": "port",
-                         "sample": "%d back-to-back passes of oracle/ref_replay (C replay of the reference's NVML call sequence: "
-                                   "%d NVML calls + %d dlopen cycles per pass, nvmlInit/Shutdown every pass); the Go reference "
-                                   "cannot be built on this image" % (len(ms), r["nvml_calls"], r["dl_cycles"]),
-                         "init_ms": round(sum(r["init_ms"][args.warmup:]) / len(ms), 4)},
-        "e2e": {"value": round(e2e_ms, 4), "unit": "ms", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0, "mean": round(sum(e2e) / len(e2e), 4),
-                "note": "MEDIAN over the K steps of exec->exit of a one-shot oracle/ref_replay run + reading the label file (process spawns on "
-                        "this box have 40-270 ms outliers for either arm: profiles/r1c_e2e_context_1gpu.txt)"},
-        "gpu_launches": 0, "labeling_pass_ms_spread": spread,
-    }
-    print(json.dumps(line), flush=True)
-    return 0
-
-
-def reduce_over_ranks(pass_ms, e2e_ms, kernel_ms, probe_gbps, host_gbps, world, device):
-    """Times: MAX over ranks (the node pass runs on rank 0 only, the others contribute 0).  Probe bandwidths: SUM over
-    ranks (one GPU each).  No data-path collective exists; this is result plumbing (NCCL on GPUs, gloo in the CPU test)."""
-    if world <= 1:
-        return pass_ms, e2e_ms, kernel_ms, probe_gbps, host_gbps
-    import torch
-    import torch.distributed as dist
-    t = torch.tensor([pass_ms, e2e_ms, kernel_ms], device=device, dtype=torch.float64)
-    dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    g = torch.tensor([probe_gbps, host_gbps], device=device, dtype=torch.float64)
-    dist.all_reduce(g, op=dist.ReduceOp.SUM)
-    a, b = [float(x) for x in t.cpu()], [float(x) for x in g.cpu()]
-    return a[0], a[1], a[2], b[0], b[1]
 
 
 def persistence_mode():
@@ -214,14 +209,117 @@ def persistence_mode():
         return "unknown"
 
 
-def workload_config():
-    return {"persistence_mode": persistence_mode(), "workload": "BASELINE configs[1]: B200 node, MIG strategy none, --no-timestamp, full label set from the real NVML + "
+def node_gpu_count():
+    """GPUs NVML attaches at nvmlInit_v2 on this node (every GPU the container shows, whatever --gpus says)."""
+    try:
+        p = subprocess.run(["nvidia-smi", "-L"], capture_output=True, text=True, timeout=30)
+        return sum(1 for l in p.stdout.splitlines() if l.startswith("GPU ")) if p.returncode == 0 else None
+    except Exception:
+        return None
+
+
+def workload_config(gpus, node_gpus, gpus_labelled):
+    return {"persistence_mode": persistence_mode(),
+            "workload": "BASELINE configs[1]: B200 node, MIG strategy none, --no-timestamp, full label set from the real NVML + "
                         "vGPU sysfs scan + atomic file write; one step = one labeling pass",
+            "gpus_labelled": gpus_labelled, "node_gpus": node_gpus,
+            "device_cap": "GFD_B200_BENCH_MAX_DEVICES=%d in both arms (first N device indices; nvmlInit_v2 still attaches all %s GPUs "
+                          "of the node, so its share of the pass does not shrink with N)" % (gpus, node_gpus),
+            "statistic": "value = MEDIAN of the K timed passes, ms_per_step = their mean; W warm-up passes untimed; passes run in "
+                         "processes of %d timed passes (+1 untimed process warm-up pass each)" % CHUNK,
             "probe": "opt-in hbm_read_fold, %d MiB per launch (input >> 126 MB L2, so no L2 flush between iterations)" % (PROBE_BYTES >> 20),
-            "parallelism": "the pass is per node: rank 0 labels all N GPUs (one host thread per GPU), no collective; probes are per-GPU replicas",
-            "multi_rank_note": "with N > 1 the waiting ranks hold CUDA contexts on their GPUs (parked in a host-side gloo barrier), and a GPU that is "
-                               "already held open makes nvmlInit_v2 cheaper (profiles/r1c_pass_spread_8xB200.txt); the reference arm's other ranks "
-                               "exit at once, so its node is idle: the like-for-like comparison is the N = 1 line"}
+            "parallelism": "the pass is per node: rank 0 labels the first N GPUs (one host thread per GPU), no collective; probes are "
+                           "per-GPU replicas; P2P = one kernel per directed pair, no NCCL",
+            "node_state": "no rank holds a CUDA context while the passes and one-shot runs are timed (gloo barriers; CUDA + NCCL start "
+                          "afterwards), same as under --impl reference"}
+
+
+def reference_arm(args, rank, world):
+    """oracle/ref_replay alone: the same series shape, statistic, device cap and e2e definition as the product arm."""
+    if rank != 0:
+        return 0
+    tmp = tempfile.mkdtemp(prefix="gfd-bench-")
+    out = os.path.join(tmp, "gfd")
+    env = bench_env(args.gpus)
+    last = {}
+
+    def run(n):
+        rows, r = replay_passes(n, out, env)
+        last.update(r)
+        return rows
+    rows, _ = series(args.warmup, args.steps, run)
+    st, phases = stats(rows)
+    labelled = gpu_count_label(open(out).read())
+    e2e = []
+    for i in range(args.warmup + args.steps):
+        dt, _ = oneshot(replay_oneshot_argv(out), out, env)
+        if i >= args.warmup:
+            e2e.append(dt)
+    e2e_ms = statistics.median(e2e)
+    line = {
+        "impl": "reference", "metric": "labeling_pass_ms", "value": st["median"], "unit": "ms", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": st["mean"], "higher_is_better": False, "scaling": "weak",
+        "vs_baseline": None, "dtype": "u64", "data": "real NVML of this host (no synthetic input: the pass reads the driver)",
+        "config": workload_config(args.gpus, node_gpu_count(), labelled),
+        "cpu_baseline": {"value": st["median"], "unit": "ms", "cores": 1, "kind": "port",
+                         "sample": "%d passes of oracle/ref_replay (C replay of the reference's NVML call sequence: "
+                                   "%d NVML calls + %d dlopen cycles per pass, nvmlInit/Shutdown every pass); the Go reference "
+                                   "cannot be built on this image" % (st["n"], last["nvml_calls"], last["dl_cycles"]),
+                         "phases_ms": phases},
+        "e2e": {"value": round(e2e_ms, 4), "unit": "ms", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0, "mean": round(sum(e2e) / len(e2e), 4),
+                "note": "MEDIAN over the K steps of exec->exit of a one-shot oracle/ref_replay run + reading the label file (process spawns on "
+                        "this box have 40-270 ms outliers for either arm: profiles/r1c_e2e_context_1gpu.txt)"},
+        "gpu_launches": 0, "labeling_pass_ms_spread": st,
+    }
+    print(json.dumps(line), flush=True)
+    return 0
+
+
+def reduce_over_ranks(pass_ms, e2e_ms, kernel_ms, probe_gbps, host_gbps, world, device, group=None):
+    """Times: MAX over ranks (the node pass runs on rank 0 only, the others contribute 0).  Probe bandwidths: SUM over
+    ranks (one GPU each).  No data-path collective exists; this is result plumbing (NCCL on GPUs, gloo in the CPU test)."""
+    if world <= 1:
+        return pass_ms, e2e_ms, kernel_ms, probe_gbps, host_gbps
+    import torch
+    import torch.distributed as dist
+    t = torch.tensor([pass_ms, e2e_ms, kernel_ms], device=device, dtype=torch.float64)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX, group=group)
+    g = torch.tensor([probe_gbps, host_gbps], device=device, dtype=torch.float64)
+    dist.all_reduce(g, op=dist.ReduceOp.SUM, group=group)
+    a, b = [float(x) for x in t.cpu()], [float(x) for x in g.cpu()]
+    return a[0], a[1], a[2], b[0], b[1]
+
+
+def p2p_section(B, n, bytes_per_direction=1 << 30, warmup=2, iters=10):
+    """Kernel B under the driver: all n*(n-1) directed pairs of the first n GPUs, tournament schedule (both directions of every
+    pair at once), peer loads (READ, what --probe-nvlink's read label reports) and peer stores (PUSH).  gfd_probe_p2p_matrix
+    verifies every transfer against the pattern's checksum and fails with GFD_ERR_DATA_MISMATCH otherwise, so reaching the
+    return IS verified = true.  -> (roofline_p2p object, kernel launches made)."""
+    out, launches = {}, 0
+    m_even = n if n % 2 == 0 else n + 1
+    for mode, name in ((B.PROBE_READ, "read"), (B.PROBE_PUSH, "push")):
+        m, ring = B.probe_p2p_matrix(n, bytes_per_direction, warmup=warmup, iters=iters, mode=mode)
+        off = [m[a][b] for a in range(n) for b in range(n) if a != b]
+        out[name] = {"bound": "nvlink", "achieved_per_direction_min": round(min(off), 1), "achieved_per_direction_max": round(max(off), 1),
+                     "achieved_ring_aggregate": round(ring, 1), "peak": 900.0, "unit": "GB/s", "frac": round(min(off) / 900.0, 4),
+                     "mode": name, "pairs": n * (n - 1), "verified": True, "bytes_per_direction_per_launch": bytes_per_direction,
+                     "iters": iters, "schedule": "%d rounds x %d disjoint pairs, both directions at once; then an all-GPU ring" % (m_even - 1, n // 2)}
+        per_round = (n if n % 2 == 0 else n - 1) * (warmup + iters)
+        verify = (n if n % 2 == 0 else n - 1) if mode != B.PROBE_READ else 0
+        launches += 2 * n + (m_even - 1) * (per_round + verify) + n * (warmup + iters) + (n if mode != B.PROBE_READ else 0)
+    top = dict(out["read"])
+    top["push"] = out["push"]
+    top["verified"] = out["read"]["verified"] and out["push"]["verified"]
+    top["peak_source"] = "NVLink 5 nominal, 900 GB/s per direction per GPU (B200_PROFILING.md); kernels: hbm_read_fold_kernel<peer>, hbm_copy_kernel"
+    return top, launches
+
+
+def gpu_count_label(text):
+    """nvidia.com/gpu.count of a label file = how many GPUs the pass labelled."""
+    for l in text.splitlines():
+        if l.startswith("nvidia.com/gpu.count="):
+            return int(l.split("=", 1)[1])
+    return None
 
 
 def main():
@@ -243,63 +341,82 @@ def main():
     import torch
     import torch.distributed as dist
     B = importlib.import_module("gpu-feature-discovery_b200.binding")  # raises if libgfd_b200.so is missing: no fallback
+    if not os.path.exists("/dev/nvidiactl"):  # asked of the file system: no CUDA call (and no context) before the passes are done
+        raise SystemExit("bench.py needs a GPU: the product path has no CPU fallback")
+    if world > 1:
+        # Host-side group first.  Barriers go over gloo (TCP): an NCCL barrier is a kernel that SPINS on every waiting rank's
+        # GPU, and rank 0's labeling passes attach to exactly those GPUs through NVML meanwhile (2 GPUs: pass median 50 ms
+        # with the other rank parked in an NCCL barrier, 21-30 ms without).  More than that: until region A and the one-shot
+        # runs are over NO rank touches CUDA at all, so the node looks exactly as it does under --impl reference.
+        os.environ.setdefault("GLOO_SOCKET_IFNAME", "lo")  # one node: loopback always exists, the hostname may not resolve
+        dist.init_process_group("gloo")
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+
+    tmp = tempfile.mkdtemp(prefix="gfd-bench-r%d-" % rank)
+    out_file, replay_out = os.path.join(tmp, "gfd"), os.path.join(tmp, "replay")
+    env = bench_env(args.gpus)
+    node_gpus = node_gpu_count() if rank == 0 else None
+    cfg_line = workload_config(args.gpus, node_gpus, None) if rank == 0 else None  # asks nvidia-smi: before any timed region
+
+    # ---- region A: K labeling passes inside the running labeler, interleaved with the CPU baseline's -------------
+    # The pass is per NODE (one labeler per node is the deployment: a DaemonSet pod), so with N ranks it is rank 0
+    # that runs it -- once, over the first N GPUs, with the labeler's own per-GPU host threads -- while the other ranks
+    # wait at the barrier.  N copies of a node-level daemon hammering one driver would measure contention, not GFD.
+    barrier()
+    pass_ms = e2e_ms = 0.0
+    prod_st = prod_ph = rep_st = rep_ph = keep_st = None
+    e2e_stats, rep_info, product_text, replay_text = {}, {}, "", ""
+    if rank == 0:
+        def run_replay(n):
+            rows, r = replay_passes(n, replay_out, env)
+            rep_info.update(r)
+            return rows
+        prod_rows, rep_rows = series(args.warmup, args.steps, lambda n: product_passes(B.BIN_PATH, n, out_file, env), run_replay)
+        prod_st, prod_ph = stats(prod_rows)
+        rep_st, rep_ph = stats(rep_rows)
+        pass_ms = prod_st["median"]
+        product_text, replay_text = open(out_file).read(), open(replay_out).read()
+        # ---- e2e: the user-facing call, exec -> exit + read the file back; the two arms alternate run by run ----
+        e2e, e2e_rep = [], []
+        for i in range(args.warmup + args.steps):
+            dt, _ = oneshot(product_oneshot_argv(B.BIN_PATH, out_file), out_file, env)
+            dr, _ = oneshot(replay_oneshot_argv(replay_out), replay_out, env)
+            if i >= args.warmup:
+                e2e.append(dt)
+                e2e_rep.append(dr)
+        e2e_ms = statistics.median(e2e)
+        e2e_stats = {"mean": round(sum(e2e) / len(e2e), 4), "cpu_baseline_median": round(statistics.median(e2e_rep), 4),
+                     "cpu_baseline_mean": round(sum(e2e_rep) / len(e2e_rep), 4)}
+        keep_rows = product_passes(B.BIN_PATH, args.warmup + args.steps, out_file, env, extra=["--keep-nvml-attached"])[args.warmup:]
+        keep_st, _ = stats(keep_rows)
+    barrier()
+
+    # ---- only now: CUDA, and NCCL for the result reduction ------------------------------------------------------------
     if not torch.cuda.is_available():
         raise SystemExit("bench.py needs a GPU: the product path has no CPU fallback")
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
-    host_group = None
+    nccl = None
     if world > 1:
-        dist.init_process_group("nccl", device_id=dev)
-        # Barriers go over a gloo (TCP) group: an NCCL barrier is a kernel that SPINS on every waiting rank's GPU (and a
-        # polling host thread), and rank 0's labeling passes attach to exactly those GPUs through NVML meanwhile --
-        # measured on 2 GPUs: pass median 50 ms with the other rank parked in an NCCL barrier, 21-30 ms without.
-        os.environ.setdefault("GLOO_SOCKET_IFNAME", "lo")  # one node: loopback always exists, the hostname may not resolve
         try:
-            if os.environ.get("GFD_BENCH_FILE_BARRIER"):  # test knob: exercise the fallback
-                raise RuntimeError("forced by GFD_BENCH_FILE_BARRIER")
-            host_group = dist.new_group(backend="gloo")
-        except Exception as e:  # no gloo transport: fall back to a barrier through the node's file system
-            print("bench: gloo group unavailable (%s); using a file barrier" % e, file=sys.stderr)
-    token = [tempfile.mkdtemp(prefix="gfd-bench-barrier-") if rank == 0 else None]
-    if world > 1 and host_group is None:
-        dist.broadcast_object_list(token, src=0)
-    barrier_no = [0]
+            nccl = dist.new_group(backend="nccl", device_id=dev)
+        except TypeError:  # older signature
+            nccl = dist.new_group(backend="nccl")
 
-    def barrier():
+    def gpu_barrier():
         torch.cuda.synchronize()
-        if world > 1 and host_group is not None:
-            dist.barrier(group=host_group)
-        elif world > 1:
-            barrier_no[0] += 1
-            open(os.path.join(token[0], "%d.%d" % (barrier_no[0], rank)), "w").close()
-            while not all(os.path.exists(os.path.join(token[0], "%d.%d" % (barrier_no[0], r))) for r in range(world)):
-                time.sleep(0.001)
+        barrier()
         torch.cuda.synchronize()
-
-    tmp = tempfile.mkdtemp(prefix="gfd-bench-r%d-" % rank)
-    out_file = os.path.join(tmp, "gfd")
-
-    # ---- region A: K labeling passes inside the running labeler (W warm-up passes first) ----------------------
-    # The pass is per NODE (one labeler per node is the deployment: a DaemonSet pod), so with N ranks it is rank 0
-    # that runs it -- once, over all N GPUs, with the labeler's own per-GPU host threads -- while the other ranks
-    # wait at the barrier.  N copies of a node-level daemon hammering one driver would measure contention, not GFD.
-    barrier()
-    pass_ms, product_text, phases, pass_stats = 0.0, "", {}, {}
-    if rank == 0:
-        ms = product_passes(B.BIN_PATH, args.warmup + args.steps, out_file)[args.warmup:]
-        pass_ms = sum(ms) / len(ms)
-        pass_stats = {"median": round(statistics.median(ms), 4), "min": round(min(ms), 4), "max": round(max(ms), 4)}
-        phases = dict(PHASES)
-        product_text = open(out_file).read()
-    barrier()
 
     # ---- region B: K launches of the dominant kernel, CUDA events on the launching stream ---------------------
     buf = torch.empty(PROBE_BYTES, dtype=torch.uint8, device=dev)
     scratch = torch.empty(B.hbm_scratch_bytes(), dtype=torch.uint8, device=dev)
-    B.hbm_scratch_init(scratch.data_ptr(), scratch.numel(), torch.cuda.current_stream().cuda_stream)  # once; no per-call memset
-    torch.cuda.synchronize()
-    d_out = torch.zeros(2, dtype=torch.int64, device=dev)
     stream = torch.cuda.current_stream()
+    B.hbm_scratch_init(scratch.data_ptr(), scratch.numel(), stream.cuda_stream)  # once per scratch; nothing is cleared per call
+    d_out = torch.zeros(2, dtype=torch.int64, device=dev)
     B.hbm_fill_pattern(buf.data_ptr(), PROBE_BYTES, 0, stream.cuda_stream)
     launches = 1
     # clocks are sampled around the GPU region only: nvidia-smi is itself an NVML client, and polling it while the
@@ -309,15 +426,15 @@ def main():
     time.sleep(0.3)
     for _ in range(args.warmup):
         B.hbm_read_checksum(buf.data_ptr(), PROBE_BYTES, d_out.data_ptr(), scratch.data_ptr(), scratch.numel(), stream.cuda_stream)
-        launches += 1
-    barrier()
+        launches += 1  # one kernel per checksum: the last CTA finishes (no memset, no finishing kernel)
+    gpu_barrier()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record(stream)
     for _ in range(args.steps):
         B.hbm_read_checksum(buf.data_ptr(), PROBE_BYTES, d_out.data_ptr(), scratch.data_ptr(), scratch.numel(), stream.cuda_stream)
         launches += 1
     e1.record(stream)
-    barrier()
+    gpu_barrier()
     # keep the GPU under the same load a little longer so the 100 ms sampler sees clocks under load
     t_hold = time.time()
     while time.time() - t_hold < 0.5:
@@ -327,20 +444,8 @@ def main():
     kernel_ms = e0.elapsed_time(e1) / args.steps
     probe_gbps = PROBE_BYTES / (kernel_ms * 1e-3) / 1e9
     checksum = tuple(int(v) for v in d_out.cpu().numpy().view(np.uint64))
-
     sampler.stop()
     clocks = sampler.summary()
-
-    # ---- e2e: the user-facing call, exec -> exit + read the file back ----------------------------------------
-    e2e_ms = e2e_mean = 0.0
-    if rank == 0:
-        e2e = []
-        for i in range(args.warmup + args.steps):
-            dt, data = product_oneshot(B.BIN_PATH, out_file)
-            if i >= args.warmup:
-                e2e.append(dt)
-        e2e_ms, e2e_mean = statistics.median(e2e), sum(e2e) / len(e2e)
-    barrier()
 
     # host-buffer form of the probe kernel through the C ABI (pinned host memory; copies inside the timed region)
     host_bytes = 1 << 30
@@ -349,78 +454,99 @@ def main():
     reps = 5
     for _ in range(2):
         B.checksum_host(local_rank, pinned.data_ptr(), host_bytes)
-    launches += 1 * (2 + reps)  # gfd_checksum_host = hbm_read_fold + fold_finish per call
+    launches += 2 + reps  # gfd_checksum_host = one hbm_read_fold launch per call
     t0 = time.perf_counter()
     for _ in range(reps):
-        host_sum = B.checksum_host(local_rank, pinned.data_ptr(), host_bytes)
+        B.checksum_host(local_rank, pinned.data_ptr(), host_bytes)
     host_gbps = host_bytes * reps / (time.perf_counter() - t0) / 1e9
+    gpu_barrier()
+
+    # ---- region C (N >= 2): the NVLink probe kernels over all directed pairs of the N GPUs, driven by rank 0 ----------
+    # One kernel per directed pair, peer-mapped loads / stores, no NCCL (nothing is reduced).  The other ranks idle at the
+    # barrier; their probe buffers are freed first so that every GPU has room for the pair buffers.
+    del buf, pinned
+    torch.cuda.empty_cache()
+    gpu_barrier()
+    roofline_p2p = None
+    if world > 1 and rank == 0:
+        n_p2p = min(world, torch.cuda.device_count())
+        if n_p2p >= 2:
+            roofline_p2p, p2p_launches = p2p_section(B, n_p2p)
+            launches += p2p_launches
+    gpu_barrier()
 
     # ---- reductions over ranks --------------------------------------------------------------------------------
     pass_ms, e2e_ms, kernel_ms, probe_total, host_total = reduce_over_ranks(pass_ms, e2e_ms, kernel_ms, probe_gbps, host_gbps,
-                                                                             world, dev)
-
+                                                                             world, dev, nccl)
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
         return 0
 
-    # ---- rank 0 only: checker + CPU baseline (the oracle is the checker / the baseline, never the thing measured) ----
+    # ---- rank 0 only: the checker (the oracle is the checker / the baseline, never the thing measured) ----------------
     from oracle import gfd_oracle as O, nvml_model as M
     cfg = O.Config(mig_strategy="none", no_timestamp=True)
+    labelled = gpu_count_label(product_text)
     try:
-        want, _ = O.run_pass(O.NvmlManager(M.PynvmlRaw()), lambda: O.nvidia_pci_devices(), cfg)
+        raw = M.PynvmlRaw()
+        if node_gpus and args.gpus < node_gpus:  # the same cap the two arms ran under
+            full_count = raw.device_get_count
+            raw.device_get_count = lambda: (lambda rc, v: (rc, min(v, args.gpus) if rc == 0 else v))(*full_count())
+        want, _ = O.run_pass(O.NvmlManager(raw), lambda: O.nvidia_pci_devices(), cfg)
         oracle_text = O.render(want)
     except O.GfdError as e:
         oracle_text = "ORACLE-ERROR %s\n" % e
-    replay_out = os.path.join(tmp, "replay")
-    r = replay_passes(args.warmup + min(args.steps, 30), replay_out)
-    rms = r["ms"][args.warmup:]
-    replay_text = open(replay_out).read()
     orc = ctypes.CDLL(os.path.join(ROOT, "oracle", "libgfd_oracle_c.so"))
     orc.oracle_pattern_checksum.argtypes = [ctypes.c_size_t, ctypes.c_uint64, ctypes.POINTER(ctypes.c_uint64)]
     o = (ctypes.c_uint64 * 2)()
     orc.oracle_pattern_checksum(PROBE_BYTES // 8, 0, o)
     checksum_ok = checksum == (int(o[0]), int(o[1]))
 
-    keep = product_passes(B.BIN_PATH, args.warmup + args.steps, out_file, extra=["--keep-nvml-attached"])[args.warmup:]
-
     peak, peak_src = load_peaks()
-    traffic = None  # dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed ncu --set full capture
-    try:
-        t = json.load(open(os.path.join(ROOT, "profiles", "r1c_traffic.json")))["hbm_read_fold_kernel"]
-        if t["bytes_per_launch"] == PROBE_BYTES:
-            traffic = t["dram_bytes_read"] + t["dram_bytes_write"]
-    except Exception:
-        pass
+    traffic, traffic_src = None, None  # dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed ncu --set full capture
+    for name in ("r2_traffic.json", "r1c_traffic.json"):
+        try:
+            t = json.load(open(os.path.join(ROOT, "profiles", name)))["hbm_read_fold_kernel"]
+            if t["bytes_per_launch"] == PROBE_BYTES:
+                traffic, traffic_src = t["dram_bytes_read"] + t["dram_bytes_write"], name
+                break
+        except Exception:
+            continue
+    cfg_line["gpus_labelled"] = labelled
     line = {
         "metric": "labeling_pass_ms", "value": round(pass_ms, 4), "unit": "ms", "n_gpus": args.gpus, "steps": args.steps,
-        "warmup": args.warmup, "ms_per_step": round(pass_ms, 4), "higher_is_better": False, "scaling": "weak", "vs_baseline": None,
+        "warmup": args.warmup, "ms_per_step": prod_st["mean"], "higher_is_better": False, "scaling": "weak", "vs_baseline": None,
         "dtype": "u64", "data": "real NVML of this host (no synthetic input: the pass reads the driver); probe input = deterministic pattern",
-        "config": workload_config(),
-        "e2e": {"value": round(e2e_ms, 4), "unit": "ms", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0, "mean": round(e2e_mean, 4),
-                "note": "MEDIAN over the K steps of exec->exit of gpu-feature-discovery --oneshot + reading the label file (process spawns on this "
-                        "box have 40-270 ms outliers for either arm: profiles/r1c_e2e_context_1gpu.txt); the labeling pass moves no tensor data"},
+        "config": cfg_line,
+        "e2e": dict({"value": round(e2e_ms, 4), "unit": "ms", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0,
+                     "note": "MEDIAN over the K steps of exec->exit of gpu-feature-discovery --oneshot + reading the label file, alternating run by "
+                             "run with the same call on oracle/ref_replay (cpu_baseline_*); process spawns on this box have 40-270 ms outliers "
+                             "for either arm; the labeling pass moves no tensor data"}, **e2e_stats),
         "e2e_probe_host": {"value": round(host_total, 2), "unit": "GB/s", "h2d_bytes_per_step": host_bytes, "d2h_bytes_per_step": 16,
                            "note": "gfd_checksum_host: pinned host buffer -> HBM -> hbm_read_fold -> 16-byte result"},
         "gpu_launches": launches,
         "label_diff": {"vs_cpu_baseline": diff_lines(product_text, replay_text), "vs_oracle_pynvml": diff_lines(product_text, oracle_text),
                        "labels": len(product_text.splitlines())},
-        "labeling_pass_phases_ms": phases,
-        "labeling_pass_ms_spread": pass_stats,  # `value` is the mean over the K steps (the contract); a shared host makes single passes jump
-        "labeling_pass_ms_keep_attached": round(sum(keep) / len(keep), 4),
+        "labeling_pass_phases_ms": prod_ph,
+        "labeling_pass_ms_spread": prod_st,
+        "labeling_pass_ms_keep_attached": keep_st["median"],
         "probe_hbm_read_gbps": round(probe_total, 1),
         "probe_checksum_ok": checksum_ok,
         "roofline": {"bound": "hbm", "achieved": round(probe_gbps, 1), "peak": peak, "unit": "GB/s", "frac": round(probe_gbps / peak, 4),
-                     "traffic": traffic, "traffic_unit": "bytes per launch (ncu, profiles/r1c_ncu_full_summary.md)", "peak_source": peak_src, "kernel": "hbm_read_fold_kernel (+ 1-CTA fold_finish_kernel)",
+                     "traffic": traffic, "traffic_unit": "bytes per launch (ncu --set full, profiles/%s)" % traffic_src, "peak_source": peak_src,
+                     "kernel": "hbm_read_fold_kernel (one launch per checksum; the last CTA folds the partials)",
                      "algorithmic_bytes_per_launch": PROBE_BYTES, "ms_per_launch": round(kernel_ms, 5),
                      "frac_of_nominal_7700": round(probe_gbps / 7700.0, 4)},
-        "cpu_baseline": {"value": round(sum(rms) / len(rms), 4), "unit": "ms", "cores": 1, "kind": "port",
-                         "sample": "%d back-to-back passes of oracle/ref_replay (C replay of the reference's NVML call sequence: %d NVML "
-                                   "calls + %d dlopen cycles per pass)" % (len(rms), r["nvml_calls"], r["dl_cycles"]),
-                         "init_ms": round(sum(r["init_ms"][args.warmup:]) / len(rms), 4)},
+        "cpu_baseline": {"value": rep_st["median"], "unit": "ms", "cores": 1, "kind": "port",
+                         "sample": "%d passes of oracle/ref_replay (C replay of the reference's NVML call sequence: %d NVML calls + %d dlopen "
+                                   "cycles per pass) INTERLEAVED with the product's passes, chunks of %d, same device cap"
+                                   % (rep_st["n"], rep_info["nvml_calls"], rep_info["dl_cycles"], CHUNK),
+                         "mean": rep_st["mean"], "phases_ms": rep_ph, "spread": rep_st},
         "clocks": clocks,
         "host_cores": os.cpu_count(),
     }
+    if roofline_p2p is not None:
+        line["roofline_p2p"] = roofline_p2p
     print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()

@@ -50,7 +50,11 @@ int main(void) {
             int rc = gfd_dev_name(mig, buf, sizeof buf);
             if (rc) { printf("  mig %d: profile unresolved: %s\n", k, gfd_strerror(rc)); continue; }
             CHECK(gfd_dev_attributes(mig, &a));
-            printf("  mig %d: %s, %" PRIu64 " MiB, %u SMs, slices gi=%u ci=%u\n", k, buf, a.memory_mb, a.multiprocessors, a.slices_gi, a.slices_ci);
+            gfd_dev *parent = NULL;  /* Device.GetDeviceHandleFromMigDeviceHandle (nvml-mig-device.go:56-72) */
+            char pname[96];
+            CHECK(gfd_dev_parent(mig, &parent));
+            CHECK(gfd_dev_name(parent, pname, sizeof pname));
+            printf("  mig %d: %s, %" PRIu64 " MiB, %u SMs, slices gi=%u ci=%u, parent %s\n", k, buf, a.memory_mb, a.multiprocessors, a.slices_gi, a.slices_ci, pname);
         }
     }
     uint64_t calls = 0, probes = 0;

@@ -292,6 +292,18 @@ int device_of_pointer(const void *p, int *dev) {
     return 0;
 }
 
+// `dev` (current) is about to dereference memory of `other`: make sure the peer mapping exists.  Enabling it twice is fine.
+int ensure_peer_mapping(int dev, int other) {
+    if (dev == other) return 0;
+    int can = 0;
+    CUDA_TRY(cudaDeviceCanAccessPeer(&can, dev, other));
+    if (!can) return GFD_ERR_PEER_ACCESS;
+    cudaError_t e = cudaDeviceEnablePeerAccess(other, 0);
+    if (e == cudaErrorPeerAccessAlreadyEnabled) { (void)cudaGetLastError(); return 0; }
+    if (e != cudaSuccess) { (void)cudaGetLastError(); return GFD_ERR_CUDA + (int)e; }
+    return 0;
+}
+
 struct DeviceScope {  // this library's static CUDA runtime keeps its own current device; set + restore it
     int prev = -1;
     int rc = 0;
@@ -447,6 +459,7 @@ GFD_API int gfd_hbm_read_checksum(const void *d_buf, size_t bytes, gfd_checksum 
     if (bytes && (rc = device_of_pointer(d_buf, &src_dev))) return rc;
     DeviceScope scope(dev);
     if (scope.rc) return scope.rc;
+    if ((rc = ensure_peer_mapping(dev, src_dev))) return rc;  // a source on another GPU is read over NVLink, not faulted on
     return launch_read(dev, d_buf, bytes, d_out, d_scratch, static_cast<cudaStream_t>(stream), nullptr, src_dev != dev);
 }
 
@@ -462,6 +475,7 @@ GFD_API int gfd_hbm_copy(void *d_dst, const void *d_src, size_t bytes, void *str
     if ((rc = device_of_pointer(d_src, &src_dev))) return rc;
     DeviceScope scope(dev);
     if (scope.rc) return scope.rc;
+    if ((rc = ensure_peer_mapping(dev, src_dev))) return rc;
     return launch_copy(dev, d_dst, d_src, bytes, static_cast<cudaStream_t>(stream), nullptr, src_dev != dev);
 }
 
@@ -529,6 +543,9 @@ GFD_API int gfd_hbm_read_checksum_noalloc(const void *d_buf, size_t bytes, gfd_c
     if ((rc = device_of_pointer(d_out, &dev))) return rc;
     int src_dev = dev;
     if (bytes && (rc = device_of_pointer(d_buf, &src_dev))) return rc;  // a host or stale pointer is refused here, not faulted on
+    // Reading another GPU's memory needs a peer mapping, and setting one up is exactly the kind of driver-side resource
+    // grab this entry point promises not to make (nor can it tell whether the caller already has one): same GPU only.
+    if (src_dev != dev) return GFD_ERR_BAD_ARGUMENT;
     DeviceScope scope(dev);
     if (scope.rc) return scope.rc;
     DevInfo di;
@@ -536,7 +553,7 @@ GFD_API int gfd_hbm_read_checksum_noalloc(const void *d_buf, size_t bytes, gfd_c
     if (grid_for(di.sms, bytes / 16) > kNoAllocMaxBlocks - 1) return GFD_ERR_SIZE_LIMIT;  // slot 0 is the header
     void *scratch = nullptr;
     if ((rc = noalloc_scratch(dev, &scratch))) return rc;
-    return launch_read(dev, d_buf, bytes, d_out, scratch, static_cast<cudaStream_t>(stream), nullptr, src_dev != dev);
+    return launch_read(dev, d_buf, bytes, d_out, scratch, static_cast<cudaStream_t>(stream), nullptr);
 }
 
 // ---- host-buffer form ---------------------------------------------------------------------------------

@@ -24,12 +24,20 @@ namespace gfdlm {
 namespace {
 
 const char *kFullGpuResource = "nvidia.com/gpu";  // internal/lm/resource.go:27
-bool g_current_tables = false;                      // --current-tables (opt-in), set per pass by nvml_labels
 
 [[noreturn]] void fail(const std::string &what, int status) {
     throw PassError(what + ": " + gfd_strerror(status));
 }
 [[noreturn]] void fail(const std::string &what) { throw PassError(what); }
+// fmt.Errorf("<prefix>: %v", err) around a callee, so that the logged error chain reads like the reference's
+template <class F>
+void wrapped(const char *prefix, F &&fn) {
+    try {
+        fn();
+    } catch (const PassError &e) {
+        throw PassError(std::string(prefix) + ": " + e.what());
+    }
+}
 
 // os.ReadFile: whole file or an error (directories and unreadable files are errors; empty files are not)
 bool read_file(const std::string &path, std::string *out, std::string *err) {
@@ -138,7 +146,7 @@ const char *arch_family(int major, int minor, bool current_tables) {
 }
 
 // NewGPUResourceLabeler (resource.go:36-73)
-void gpu_resource_labels(Labels &out, const gfdcfg::Config *config, gfd_dev *device, int count) {
+void gpu_resource_labels(Labels &out, const gfdcfg::Config *config, gfd_dev *device, int count, bool current_tables) {
     if (count == 0) return;
     std::string model = dev_name(device, "failed to get device model");
     uint64_t total_mb = dev_memory_mb(device, "failed to get memory info for device");
@@ -149,7 +157,7 @@ void gpu_resource_labels(Labels &out, const gfdcfg::Config *config, gfd_dev *dev
     rl.base(out, count, {model});
     if (total_mb != 0) out[rl.key("memory")] = std::to_string(total_mb);
     if (major != 0) {  // newArchitectureLabels (resource.go:239-258)
-        out[rl.key("family")] = arch_family(major, minor, g_current_tables);
+        out[rl.key("family")] = arch_family(major, minor, current_tables);
         out[rl.key("compute.major")] = std::to_string(major);
         out[rl.key("compute.minor")] = std::to_string(minor);
     }
@@ -206,7 +214,7 @@ struct DeviceInfo {
 // newGPULabelers (mig-strategy.go:113-179).  Go ranges over two maps here; on a heterogeneous node the
 // winner of nvidia.com/gpu.* is therefore random in the reference.  We iterate model names in sorted order.
 void gpu_labels(Labels &out, const DeviceInfo &di, const gfdcfg::Config &config) {
-    if (!di.any) fail("failed to construct GPU labeler: no GPU devices detected");
+    if (!di.any) fail("no GPU devices detected");
     std::map<std::string, int> counts;
     std::map<std::string, gfd_dev *> mig_enabled, full;
     for (gfd_dev *d : di.enabled) { std::string n = dev_name(d, "error getting device name"); mig_enabled[n] = d; counts[n]++; }
@@ -216,8 +224,10 @@ void gpu_labels(Labels &out, const DeviceInfo &di, const gfdcfg::Config &config)
         for (auto &kv : counts) names += (names.empty() ? "" : " ") + kv.first;
         logf("WARNING: Multiple device types detected: [%s]", names.c_str());
     }
-    for (auto &kv : mig_enabled) gpu_resource_labels(out, nullptr, kv.second, counts[kv.first]);  // WithoutSharing
-    for (auto &kv : full) gpu_resource_labels(out, &config, kv.second, counts[kv.first]);
+    wrapped("failed to construct labeler", [&] {  // mig-strategy.go:162,173
+        for (auto &kv : mig_enabled) gpu_resource_labels(out, nullptr, kv.second, counts[kv.first], config.current_tables);  // WithoutSharing
+        for (auto &kv : full) gpu_resource_labels(out, &config, kv.second, counts[kv.first], config.current_tables);
+    });
 }
 
 // newInvalidMigStrategyLabeler (mig-strategy.go:243-262)
@@ -239,7 +249,9 @@ struct MigResource {  // migResource (mig-strategy.go:37-43)
 
 std::map<std::string, MigResource> group_migs(const DeviceInfo &di, bool mixed) {
     std::map<std::string, MigResource> resources;
-    for (gfd_dev *m : di.all_migs()) {
+    std::vector<gfd_dev *> migs;
+    wrapped("unable to retrieve list of MIG devices", [&] { migs = di.all_migs(); });  // mig-strategy.go:210-213,270-273
+    for (gfd_dev *m : migs) {
         std::string n = dev_name(m, "unable to get MIG device name: failed to get MIG profile");
         auto it = resources.find(n);
         if (it == resources.end())
@@ -249,32 +261,48 @@ std::map<std::string, MigResource> group_migs(const DeviceInfo &di, bool mixed) 
     return resources;
 }
 
+// newMIGDeviceLabelers (mig-strategy.go:297-309)
+void mig_device_labels(Labels &out, const std::map<std::string, MigResource> &resources, const gfdcfg::Config &config) {
+    wrapped("failed to construct labeler", [&] {
+        for (auto &kv : resources) mig_resource_labels(out, kv.second.resource_name, &config, kv.second.device, kv.second.count);
+    });
+}
+
 // newMigStrategySingleLabeler (mig-strategy.go:181-241)
 void single_labels(Labels &out, const DeviceInfo &di, const gfdcfg::Config &config) {
     if (di.enabled.empty()) return;
-    if (di.any_enabled_is_empty()) return invalid_single_labels(out, di.enabled[0], "at least one MIG device is enabled but empty");
+    bool has_empty = false;
+    wrapped("failed to check for empty MIG-enabled devices", [&] { has_empty = di.any_enabled_is_empty(); });
+    if (has_empty) return invalid_single_labels(out, di.enabled[0], "at least one MIG device is enabled but empty");
     if (!di.disabled.empty()) return invalid_single_labels(out, di.enabled[0], "devices with MIG enabled and disable detected");
     auto resources = group_migs(di, false);
     if (resources.size() != 1) return invalid_single_labels(out, di.enabled[0], "more than one MIG device type present on node");
-    for (auto &kv : resources) mig_resource_labels(out, kv.second.resource_name, &config, kv.second.device, kv.second.count);
+    mig_device_labels(out, resources, config);
 }
 
 // newMigStrategyMixedLabeler (mig-strategy.go:264-295)
 void mixed_labels(Labels &out, const DeviceInfo &di, const gfdcfg::Config &config) {
-    for (auto &kv : group_migs(di, true)) mig_resource_labels(out, kv.second.resource_name, &config, kv.second.device, kv.second.count);
+    mig_device_labels(out, group_migs(di, true), config);
 }
 
 // NewResourceLabeler (mig-strategy.go:45-77) + newMigLabeler (:84-110) + migStrategyLabeler (strategy.go:20-28)
 void resource_labels(Labels &out, Manager &mgr, const gfdcfg::Config &config) {
-    if (mgr.devices().empty()) return;
-    DeviceInfo di(mgr);
-    gpu_labels(out, di, config);
+    bool none = true;
+    wrapped("error getting devices", [&] { none = mgr.devices().empty(); });
+    if (none) return;
+    std::unique_ptr<DeviceInfo> di;
+    wrapped("failed to construct GPU labeler", [&] {
+        wrapped("error getting map of devices", [&] { di.reset(new DeviceInfo(mgr)); });  // mig.go:41-64 via mig-strategy.go:116-119
+        gpu_labels(out, *di, config);
+    });
     const std::string &s = *config.mig_strategy;
     if (s == "none") return;
     Labels mig;
-    if (s == "single") single_labels(mig, di, config);
-    else if (s == "mixed") mixed_labels(mig, di, config);
-    else fail("failed to construct MIG resource labeler: unknown strategy: " + s);
+    wrapped("failed to construct MIG resource labeler", [&] {
+        if (s == "single") wrapped("failed to create labeler for mig-strategy=single", [&] { single_labels(mig, *di, config); });
+        else if (s == "mixed") wrapped("failed to create labeler for mig-strategy=mixed", [&] { mixed_labels(mig, *di, config); });
+        else fail("unknown strategy: " + s);
+    });
     out["nvidia.com/mig.strategy"] = s;
     for (auto &kv : mig) out[kv.first] = kv.second;
 }
@@ -426,7 +454,6 @@ Labels nvml_labels(Manager &mgr, const gfdcfg::Config &config, PhaseTimes *times
         }
     } guard{mgr, t, +now};
     Labels out;
-    g_current_tables = config.current_tables;
     try {
         double t1 = now();
         mgr.prefetch(config.prefetch_threads);  // 0 = one host thread per GPU (no-op on 0/1-GPU nodes), 1 = serial
@@ -556,21 +583,36 @@ Labels probe_labels(const gfdcfg::Config &config) {
     if (config.probe_nvlink && n >= 2) {
         // all directed pairs, concurrently: n-1 rounds of n/2 disjoint pairs, both directions at once
         size_t bytes = (size_t)std::min<int64_t>(config.probe_bytes, 1ll << 30);
+        // Two figures per node, each the MINIMUM over all directed pairs under that schedule, each transfer verified against the
+        // pattern's checksum: what a kernel's peer LOADS get (p2p-read) and what its peer STORES get (p2p-write).  With both
+        // directions of a link busy they differ: a load puts a request packet on the opposite direction for every response
+        // it receives (nvltx bytes on the pulling GPU, profiles/r2_ncu_p2p_summary.md), a posted store does not.
         std::vector<double> m((size_t)n * n, 0.0);
-        double ring = 0.0;
+        double ring = 0.0, ring_w = 0.0;
+        auto min_pair = [&](int *pairs) {
+            double pmin = 1e30;
+            *pairs = 0;
+            for (int a = 0; a < n; a++)
+                for (int b = 0; b < n; b++)
+                    if (a != b && m[(size_t)a * n + b] > 0) { pmin = std::min(pmin, m[(size_t)a * n + b]); (*pairs)++; }
+            return pmin;
+        };
         rc = probe_p2p_matrix(n, bytes, 2, 10, GFD_PROBE_READ, m.data(), &ring);
         if (rc == GFD_ERR_PEER_ACCESS) {
             out["nvidia.com/gpu.probe.nvlink.pairs"] = "0";
         } else {
             if (rc) fail("NVLink probe failed", rc);
-            double pmin = 1e30;
             int pairs = 0;
-            for (int a = 0; a < n; a++)
-                for (int b = 0; b < n; b++)
-                    if (a != b && m[(size_t)a * n + b] > 0) { pmin = std::min(pmin, m[(size_t)a * n + b]); pairs++; }
+            double rmin = min_pair(&pairs);
             out["nvidia.com/gpu.probe.nvlink.pairs"] = std::to_string(pairs);
-            if (pairs) out["nvidia.com/gpu.probe.nvlink.p2p-read-gbps"] = std::to_string((long long)pmin);
+            if (pairs) out["nvidia.com/gpu.probe.nvlink.p2p-read-gbps"] = std::to_string((long long)rmin);
             out["nvidia.com/gpu.probe.nvlink.ring-gbps"] = std::to_string((long long)ring);
+            std::fill(m.begin(), m.end(), 0.0);
+            rc = probe_p2p_matrix(n, bytes, 2, 10, GFD_PROBE_PUSH, m.data(), &ring_w);
+            if (rc) fail("NVLink write probe failed", rc);
+            int wpairs = 0;
+            double wmin = min_pair(&wpairs);
+            if (wpairs) out["nvidia.com/gpu.probe.nvlink.p2p-write-gbps"] = std::to_string((long long)wmin);
         }
     }
     return out;

@@ -231,7 +231,8 @@ size_t gfd_hbm_scratch_bytes(void);
  * whose last user was killed mid-launch or raced with another. */
 int gfd_hbm_scratch_init(void *d_scratch, size_t scratch_bytes, void *stream);
 /* hbm_read_probe: stream `bytes` from HBM with 128-bit coalesced loads and fold them into *d_out
- * (device memory).  Algorithmic traffic: `bytes` read.  d_scratch: gfd_hbm_scratch_bytes() bytes, initialised once
+ * (device memory; the kernel runs on d_out's GPU -- a d_buf on another GPU is pulled over NVLink, the peer mapping being
+ * enabled on first use, GFD_ERR_PEER_ACCESS if the pair has none).  Algorithmic traffic: `bytes` read.  d_scratch: gfd_hbm_scratch_bytes() bytes, initialised once
  * (above).  One kernel launch on `stream`, nothing else. */
 int gfd_hbm_read_checksum(const void *d_buf, size_t bytes, gfd_checksum *d_out, void *d_scratch,
                           size_t scratch_bytes, void *stream);
@@ -252,8 +253,9 @@ int gfd_hbm_copy(void *d_dst, const void *d_src, size_t bytes, void *stream);
  *   - calls on the same GPU share the array; ones that overlap in time on the GPU corrupt each other (and may leave
  *     the header non-zero, which spoils later calls too).  Issue them on one stream or serialise them.  Nothing needs
  *     clearing between calls: the header is zero when the library is loaded and each launch zeroes it again as it ends.
- *   - d_buf is checked like gfd_hbm_read_checksum's: it must be device (or managed) memory, on the GPU of d_out or on a
- *     peer that GPU has mapped; a host pointer is refused with GFD_ERR_BAD_ARGUMENT instead of faulting the context.
+ *   - d_buf is validated before anything is launched: it must be device (or managed) memory ON THE SAME GPU as d_out.  A host
+ *     pointer, or a buffer on another GPU (reading it would need a peer mapping, which this entry point will not set up),
+ *     is refused with GFD_ERR_BAD_ARGUMENT instead of faulting the caller's context; gfd_hbm_read_checksum takes peer input.
  * Same result, bit for bit, as gfd_hbm_read_checksum.  d_buf 16-byte aligned, d_out device memory.  One kernel launch. */
 #define GFD_NOALLOC_MAX_BYTES (16ull << 30)
 int gfd_hbm_read_checksum_noalloc(const void *d_buf, size_t bytes, gfd_checksum *d_out, void *stream);

@@ -56,4 +56,52 @@ def test_reference_arm_runs_on_rank0_only(tmp_path):
     assert line["impl"] == "reference" and line["metric"] == "labeling_pass_ms" and line["unit"] == "ms" and line["n_gpus"] == 2
     assert line["higher_is_better"] is False and line["cpu_baseline"]["kind"] == "port" and line["cpu_baseline"]["cores"] == 1
     assert line["e2e"]["h2d_bytes_per_step"] == 0 and line["value"] > 0
-    assert "92 NVML calls + 9 dlopen cycles" in line["cpu_baseline"]["sample"]
+    # --gpus 2 on the 8-GPU node: the device cap makes the baseline label 2 GPUs (and the product arm runs under the same cap)
+    assert line["config"]["gpus_labelled"] == 2 and "32 NVML calls + 3 dlopen cycles" in line["cpu_baseline"]["sample"]
+    assert line["value"] == line["labeling_pass_ms_spread"]["median"] and line["labeling_pass_ms_spread"]["n"] == 3
+    r8 = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference", "--gpus", "8", "--steps", "6", "--warmup", "3"],
+                        env=dict(env, RANK="0"), capture_output=True, text=True, timeout=120)
+    line = json.loads(r8.stdout.strip().splitlines()[-1])
+    assert line["config"]["gpus_labelled"] == 8 and "92 NVML calls + 9 dlopen cycles" in line["cpu_baseline"]["sample"]
+    assert line["labeling_pass_ms_spread"]["n"] == 6 and set(line["cpu_baseline"]["phases_ms"]) == {"init", "shutdown"}
+
+
+def test_series_times_exactly_k_steps_and_alternates():
+    """W warm-up passes untimed, then exactly K timed passes in chunks, A and B alternating chunk by chunk; the first pass of
+    every process is dropped (process start-up is e2e's business)."""
+    sys.path.insert(0, ROOT)
+    import bench
+    calls = []
+
+    def mk(tag):
+        def run(n):
+            calls.append((tag, n))
+            return [(100.0 if i == 0 else 10.0 + i, {"init": 1.0}) for i in range(n)]
+        return run
+    a, b = bench.series(3, 12, mk("A"), mk("B"))
+    assert len(a) == 12 and len(b) == 12
+    assert calls == [("A", 3), ("B", 3), ("A", 6), ("B", 6), ("A", 6), ("B", 6), ("A", 3), ("B", 3)]
+    assert all(ms != 100.0 for ms, _ in a + b)
+    st, ph = bench.stats(a)
+    assert st["n"] == 12 and st["min"] == 11.0 and ph == {"init": 1.0}
+    rows = bench.parse_timing("x\n2026/11/07 00:00:00 timing: pass 17.5 ms (nvml 17.0, vgpu 0.3, write 0.2) [init 7.1, attach 8.8, labels 0.4, shutdown 2.2]\n")
+    assert rows == [(17.5, {"init": 7.1, "attach": 8.8, "labels": 0.4, "shutdown": 2.2})]
+
+
+def test_p2p_section_shape_and_launch_count():
+    sys.path.insert(0, ROOT)
+    import bench
+
+    class FakeB:
+        PROBE_READ, PROBE_PUSH = 0, 2
+
+        @staticmethod
+        def probe_p2p_matrix(n, nbytes, warmup, iters, mode):
+            base = 670.0 if mode == 0 else 705.0
+            return [[0.0 if a == b else base + a + b for b in range(n)] for a in range(n)], base * n
+    r, launches = bench.p2p_section(FakeB, 4, warmup=2, iters=10)
+    assert r["bound"] == "nvlink" and r["peak"] == 900.0 and r["pairs"] == 12 and r["verified"] is True
+    assert r["achieved_per_direction_min"] == 671.0 and r["push"]["achieved_per_direction_min"] == 706.0
+    assert r["mode"] == "read" and r["push"]["mode"] == "push" and r["achieved_ring_aggregate"] == 2680.0
+    # per mode: fill + pattern per GPU (8), 3 rounds x 4 GPUs x 12 launches (144), ring 4 x 12 (48); PUSH re-reads every destination
+    assert launches == (8 + 144 + 48) + (8 + 144 + 48 + 3 * 4 + 4)

@@ -374,3 +374,33 @@ def test_binary_mig_strategy_mixed(tmp_path):  # TestMigStrategyMixed, mig_test.
     assert labels["nvidia.com/mig.strategy"] == "mixed" and labels["nvidia.com/gpu.count"] == "1"
     assert labels["nvidia.com/gpu.product"] == "MOCKMODEL"
     assert "nvidia.com/mig-3g.20gb.count" in labels and "nvidia.com/mig-1g.5gb.count" in labels
+
+
+# ---- the logged error chain follows the reference's fmt.Errorf wrappers (internal/lm level) -----------------------------
+ERROR_CHAINS = [
+    # (node, strategy, chain as cmd/gpu-feature-discovery/main.go:84-89 logs it)
+    ("err_count", "none", "error creating NVML labeler: error getting devices: "),                                   # labeler.go:36, nvml.go:37
+    ("err_driver_version", "none", "error creating NVML labeler: failed to construct version labeler: error getting driver version: "),  # nvml.go:51,78
+    ("err_memory_on_representative_gpu", "none", "error creating NVML labeler: error creating resource labeler: failed to construct GPU labeler: "
+     "failed to construct labeler: failed to get memory info for device: "),                # nvml.go:61, mig-strategy.go:58,173, resource.go:48
+    ("err_mig_mode_gpu1", "none", "error creating NVML labeler: error creating resource labeler: failed to construct GPU labeler: "
+     "error getting map of devices: "),                                                     # mig-strategy.go:58,119
+    ("err_cc", "none", "error creating NVML labeler: error creating resource labeler: failed to construct GPU labeler: failed to construct labeler: "
+     "failed to create architecture labels: failed to determine CUDA compute capability: "),  # resource.go:58,242
+    ("err_max_mig_count", "single", "error creating NVML labeler: error creating resource labeler: failed to construct MIG resource labeler: "
+     "failed to create labeler for mig-strategy=single: failed to check for empty MIG-enabled devices: "),  # mig-strategy.go:69,95,194
+    ("err_mig_handle", "mixed", "error creating NVML labeler: error creating resource labeler: failed to construct MIG resource labeler: "
+     "failed to create labeler for mig-strategy=mixed: unable to retrieve list of MIG devices: "),           # mig-strategy.go:69,100,272
+    ("err_gi_profile_info", "single", "error creating NVML labeler: error creating resource labeler: failed to construct MIG resource labeler: "
+     "failed to create labeler for mig-strategy=single: unable to get MIG device name: failed to get MIG profile: "),  # :218, nvml-mig-device.go:99
+    ("c2_1xB200", "bogus", "error creating NVML labeler: error creating resource labeler: failed to construct MIG resource labeler: "
+     "unknown strategy: bogus"),                                                            # mig-strategy.go:69,102
+]
+
+
+@pytest.mark.parametrize("name,strategy,chain", ERROR_CHAINS, ids=["%s-%s" % c[:2] for c in ERROR_CHAINS])
+def test_error_chain_reads_like_the_reference(name, strategy, chain, tmp_path):
+    rc, got, stderr, _ = cli_pass(tmp_path, NODES[name], strategy)
+    assert rc == 1 and got is None
+    errors = [l for l in stderr.splitlines() if " Error: " in l]
+    assert errors and ("Error: " + chain) in errors[-1], errors

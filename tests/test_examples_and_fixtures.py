@@ -23,7 +23,7 @@ def test_c_consumer_walks_a_mixed_mig_node():
     p = subprocess.run([os.path.join(ROOT, "examples", "cabi_demo")], env=env, capture_output=True, text=True, timeout=60)
     assert p.returncode == 0, p.stderr
     assert "driver 575.57.08, cuda 12.9, 8 device(s)" in p.stdout
-    assert "  mig 0: 3g.90gb, 91648 MiB, 54 SMs, slices gi=3 ci=3" in p.stdout
+    assert "  mig 0: 3g.90gb, 91648 MiB, 54 SMs, slices gi=3 ci=3, parent NVIDIA B200" in p.stdout   # gfd_dev_parent
     assert "  mig 0: 1g.23gb.me, 22912 MiB" in p.stdout and "  mig 0: 7g.180gb, 182272 MiB" in p.stdout
     assert p.stdout.count("mig capable=1 enabled=0") == 4
 

@@ -252,3 +252,25 @@ def test_uuid_maps_to_cuda_ordinal(B):
     m.close()
     o = ctypes.c_int(-1)
     assert B.lib.gfd_cuda_device_by_uuid(uuid.encode(), ctypes.byref(o)) == 0 and o.value >= 0
+
+
+def test_probe_nvlink_adds_read_and_write_labels(B, tmp_path):
+    """--probe-nvlink: with peers, the minimum over all directed pairs for peer loads AND peer stores (both verified inside the
+    probe); on a single-GPU box the flag adds nothing.  The default label set never changes."""
+    import torch
+    rc, base, err = run_cli(B, tmp_path, "--mig-strategy=none")
+    assert rc == 0, err
+    rc, got, err = run_cli(B, tmp_path, "--mig-strategy=none", "--probe-nvlink", "--probe-size-mib=256")
+    assert rc == 0, err
+    extra = sorted(set(got.splitlines()) - set(base.splitlines()))
+    assert set(base.splitlines()) <= set(got.splitlines())
+    n = torch.cuda.device_count()
+    if n < 2:
+        assert extra == []
+        return
+    kv = dict(l.split("=") for l in extra)
+    assert sorted(kv) == ["nvidia.com/gpu.probe.nvlink.p2p-read-gbps", "nvidia.com/gpu.probe.nvlink.p2p-write-gbps",
+                          "nvidia.com/gpu.probe.nvlink.pairs", "nvidia.com/gpu.probe.nvlink.ring-gbps"]
+    assert int(kv["nvidia.com/gpu.probe.nvlink.pairs"]) == n * (n - 1)
+    assert 50 < int(kv["nvidia.com/gpu.probe.nvlink.p2p-read-gbps"]) < 2000
+    assert 50 < int(kv["nvidia.com/gpu.probe.nvlink.p2p-write-gbps"]) < 2000

@@ -37,3 +37,13 @@ def test_gpu_label_tests_over_simulated_mig_node(fixture, expect_mig_test, tmp_p
         assert "1 skipped" in tail and "7 passed" in tail, tail
     else:
         assert "8 passed" in tail and "skipped" not in tail, tail
+
+
+def test_gpu_f_row_tests_over_simulated_b200(tmp_path):
+    """tests/test_gpu_f_rows.py (config file + time-slicing, --current-tables, daemon loop / SIGHUP / SIGTERM) dry-run the same way."""
+    env = dict(os.environ, GFD_FAKE_NVML=os.path.join(FIX, "c2_1xB200.nvmlfix"),
+               LD_LIBRARY_PATH=B.FAKE_NVML_DIR + ":" + os.environ.get("LD_LIBRARY_PATH", ""))
+    p = subprocess.run([sys.executable, "-m", "pytest", os.path.join(ROOT, "tests", "test_gpu_f_rows.py"), "-q", "-x", "-p", "no:cacheprovider"],
+                       capture_output=True, text=True, env=env, cwd=ROOT, timeout=600)
+    assert p.returncode == 0, p.stdout[-4000:] + p.stderr[-2000:]
+    assert "9 passed" in p.stdout.strip().splitlines()[-1]

@@ -170,16 +170,20 @@ def test_second_gpu_gets_its_own_array_address(ctx):
             assert tuple(int(v) for v in out.cpu().numpy().view(np.uint64)) == want
 
 
-def test_peer_source_is_read_through_the_mapping(ctx):
-    """Input on cuda:1, result on cuda:0: the kernel runs on cuda:0 and pulls the bytes over NVLink (needs 2 GPUs with
-    peer access, which torch enables on the first cross-device copy)."""
+def test_input_on_another_gpu_is_refused_but_the_allocating_sibling_reads_it(ctx):
+    """Input on cuda:1, result on cuda:0.  The no-alloc entry point sets no peer mapping up, so it must refuse (BAD_ARGUMENT)
+    rather than launch a kernel that faults; the allocating entry point enables the mapping itself and pulls the bytes over
+    NVLink.  Runs in a fresh process too: nothing else has enabled peer access before."""
     torch, B = ctx.torch, ctx.B
     if torch.cuda.device_count() < 2 or not torch.cuda.can_device_access_peer(0, 1):
         pytest.skip("needs 2 peer-capable GPUs")
     n = (4 << 20) + 24
     host = np.random.default_rng(123).integers(0, 256, size=n, dtype=np.uint8)
     far = torch.from_numpy(host).to("cuda:1")
-    near = far.to("cuda:0")                         # makes torch enable peer access 0 <-> 1
     torch.cuda.synchronize()
-    assert noalloc_entry_point(ctx, far, n) == oracle_entry_point(ctx, host)
-    assert noalloc_entry_point(ctx, near, n) == oracle_entry_point(ctx, host)
+    with pytest.raises(B.GfdError) as ei:
+        B.hbm_read_checksum_noalloc(far.data_ptr(), n, ctx.out_new.data_ptr(), 0)
+    assert ei.value.status == B.GFD_ERR_BAD_ARGUMENT
+    assert reference_entry_point(ctx, far, n) == oracle_entry_point(ctx, host)     # peer loads, mapping enabled on demand
+    near = far.to("cuda:0")
+    assert noalloc_entry_point(ctx, near, n) == oracle_entry_point(ctx, host)      # and the GPU is fine afterwards
