@@ -32,6 +32,8 @@ TARGETS += $(BIN)
 endif
 DEMO := examples/cabi_demo
 TARGETS += $(DEMO)
+YAML_DUMP := tools/yaml_dump
+TARGETS += $(YAML_DUMP)
 
 all: $(TARGETS)
 
@@ -66,6 +68,10 @@ $(BIN): $(LABELER_SRCS) $(CORE_SRCS) $(CSRC)/gfd_internal.h $(LIB) include/gfd_b
 
 $(DEMO): examples/cabi_demo.c $(LIB) include/gfd_b200.h
 	$(CC) -O2 -Wall -Wextra -Iinclude $< -o $@ -L$(PKG) -lgfd_b200 -Wl,-rpath,'$$ORIGIN/../$(PKG)'
+
+# test helper: the labeler's YAML reader as a filter (tests/test_yaml_reader.py compares it with PyYAML)
+$(YAML_DUMP): tools/yaml_dump.cpp $(PKG)/labeler/yaml_lite.cpp $(PKG)/labeler/yaml_lite.hpp
+	$(CXX) -O1 -std=c++17 -Wall -Wextra $< $(PKG)/labeler/yaml_lite.cpp -o $@
 
 clean:
 	rm -f $(LIB) $(BIN) $(FAKE) $(FAKE_NOMIG) $(FAKE_CUDA) $(ORACLE_SO) $(REPLAY)

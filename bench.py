@@ -29,10 +29,11 @@ file write).  The reference has no GPU compute on this path, so:
 `--impl reference` times that replay alone (rank 0 only under torchrun) and prints the same line shape.
 N > 1: the pass is per node and does not shard across ranks, so rank 0 runs it once over the first N GPUs (the labeler's own
 per-GPU host threads are the multi-GPU path; GFD_B200_BENCH_MAX_DEVICES=N caps BOTH arms' enumeration, NVML ignores
-CUDA_VISIBLE_DEVICES) while every rank probes its own GPU (replicas); probe GB/s is the sum.  NO rank creates a CUDA context
-before the labeling passes and the one-shot runs are over: the process group starts on gloo (host-side barriers), CUDA and
-the NCCL group (result reduction only -- the data path has no collective) come up afterwards.  So the node is in the same
-state as under `--impl reference`, whose other ranks exit at once.
+CUDA_VISIBLE_DEVICES) while every rank probes its own GPU (replicas); probe GB/s is the sum.  NO rank creates a CUDA context,
+imports torch or asks nvidia-smi anything before the labeling passes and the one-shot runs are over (the other ranks sleep on
+a flag file); then the process group starts on gloo (host-side barriers), and CUDA and the NCCL group (result reduction only --
+the data path has no collective) come up.  So the node is in the same state as under `--impl reference`, whose other ranks
+exit at once.
 """
 import argparse
 import ctypes
@@ -230,8 +231,9 @@ def workload_config(gpus, node_gpus, gpus_labelled):
             "probe": "opt-in hbm_read_fold, %d MiB per launch (input >> 126 MB L2, so no L2 flush between iterations)" % (PROBE_BYTES >> 20),
             "parallelism": "the pass is per node: rank 0 labels the first N GPUs (one host thread per GPU), no collective; probes are "
                            "per-GPU replicas; P2P = one kernel per directed pair, no NCCL",
-            "node_state": "no rank holds a CUDA context while the passes and one-shot runs are timed (gloo barriers; CUDA + NCCL start "
-                          "afterwards), same as under --impl reference"}
+            "node_state": "while the passes and one-shot runs are timed no rank holds a CUDA context or has imported torch, and nvidia-smi has "
+                          "not been asked anything yet (other ranks sleep on a flag file; gloo, CUDA and NCCL start afterwards): the node "
+                          "is as under --impl reference"}
 
 
 def reference_arm(args, rank, world):
@@ -337,35 +339,23 @@ def main():
     if args.impl == "reference":
         return reference_arm(args, rank, world)
 
-    import numpy as np
-    import torch
-    import torch.distributed as dist
     B = importlib.import_module("gpu-feature-discovery_b200.binding")  # raises if libgfd_b200.so is missing: no fallback
     if not os.path.exists("/dev/nvidiactl"):  # asked of the file system: no CUDA call (and no context) before the passes are done
         raise SystemExit("bench.py needs a GPU: the product path has no CPU fallback")
-    if world > 1:
-        # Host-side group first.  Barriers go over gloo (TCP): an NCCL barrier is a kernel that SPINS on every waiting rank's
-        # GPU, and rank 0's labeling passes attach to exactly those GPUs through NVML meanwhile (2 GPUs: pass median 50 ms
-        # with the other rank parked in an NCCL barrier, 21-30 ms without).  More than that: until region A and the one-shot
-        # runs are over NO rank touches CUDA at all, so the node looks exactly as it does under --impl reference.
-        os.environ.setdefault("GLOO_SOCKET_IFNAME", "lo")  # one node: loopback always exists, the hostname may not resolve
-        dist.init_process_group("gloo")
-
-    def barrier():
-        if world > 1:
-            dist.barrier()
 
     tmp = tempfile.mkdtemp(prefix="gfd-bench-r%d-" % rank)
     out_file, replay_out = os.path.join(tmp, "gfd"), os.path.join(tmp, "replay")
     env = bench_env(args.gpus)
-    node_gpus = node_gpu_count() if rank == 0 else None
-    cfg_line = workload_config(args.gpus, node_gpus, None) if rank == 0 else None  # asks nvidia-smi: before any timed region
 
     # ---- region A: K labeling passes inside the running labeler, interleaved with the CPU baseline's -------------
     # The pass is per NODE (one labeler per node is the deployment: a DaemonSet pod), so with N ranks it is rank 0
-    # that runs it -- once, over the first N GPUs, with the labeler's own per-GPU host threads -- while the other ranks
-    # wait at the barrier.  N copies of a node-level daemon hammering one driver would measure contention, not GFD.
-    barrier()
+    # that runs it -- once, over the first N GPUs, with the labeler's own per-GPU host threads.  N copies of a node-level
+    # daemon hammering one driver would measure contention, not GFD.
+    # Until region A and the one-shot runs are over the node is kept exactly as it is under --impl reference: rank 0 has not
+    # imported torch, has asked nvidia-smi nothing, holds no CUDA context; the other ranks sleep on a flag file (no torch
+    # import, no process group, no context) -- an NCCL barrier would spin a kernel on the very GPUs the pass attaches to
+    # (2 GPUs: pass median 50 ms with the other rank parked in one, 21-30 ms without).
+    flag = os.path.join(tempfile.gettempdir(), "gfd-bench-%d-%s.region-a-done" % (os.getppid(), os.environ.get("MASTER_PORT", "0")))
     pass_ms = e2e_ms = 0.0
     prod_st = prod_ph = rep_st = rep_ph = keep_st = None
     e2e_stats, rep_info, product_text, replay_text = {}, {}, "", ""
@@ -374,25 +364,54 @@ def main():
             rows, r = replay_passes(n, replay_out, env)
             rep_info.update(r)
             return rows
-        prod_rows, rep_rows = series(args.warmup, args.steps, lambda n: product_passes(B.BIN_PATH, n, out_file, env), run_replay)
-        prod_st, prod_ph = stats(prod_rows)
-        rep_st, rep_ph = stats(rep_rows)
-        pass_ms = prod_st["median"]
-        product_text, replay_text = open(out_file).read(), open(replay_out).read()
-        # ---- e2e: the user-facing call, exec -> exit + read the file back; the two arms alternate run by run ----
-        e2e, e2e_rep = [], []
-        for i in range(args.warmup + args.steps):
-            dt, _ = oneshot(product_oneshot_argv(B.BIN_PATH, out_file), out_file, env)
-            dr, _ = oneshot(replay_oneshot_argv(replay_out), replay_out, env)
-            if i >= args.warmup:
-                e2e.append(dt)
-                e2e_rep.append(dr)
-        e2e_ms = statistics.median(e2e)
-        e2e_stats = {"mean": round(sum(e2e) / len(e2e), 4), "cpu_baseline_median": round(statistics.median(e2e_rep), 4),
-                     "cpu_baseline_mean": round(sum(e2e_rep) / len(e2e_rep), 4)}
-        keep_rows = product_passes(B.BIN_PATH, args.warmup + args.steps, out_file, env, extra=["--keep-nvml-attached"])[args.warmup:]
-        keep_st, _ = stats(keep_rows)
+        try:
+            prod_rows, rep_rows = series(args.warmup, args.steps, lambda n: product_passes(B.BIN_PATH, n, out_file, env), run_replay)
+            prod_st, prod_ph = stats(prod_rows)
+            rep_st, rep_ph = stats(rep_rows)
+            pass_ms = prod_st["median"]
+            product_text, replay_text = open(out_file).read(), open(replay_out).read()
+            # ---- e2e: the user-facing call, exec -> exit + read the file back; the two arms alternate run by run ----
+            e2e, e2e_rep = [], []
+            for i in range(args.warmup + args.steps):
+                dt, _ = oneshot(product_oneshot_argv(B.BIN_PATH, out_file), out_file, env)
+                dr, _ = oneshot(replay_oneshot_argv(replay_out), replay_out, env)
+                if i >= args.warmup:
+                    e2e.append(dt)
+                    e2e_rep.append(dr)
+            e2e_ms = statistics.median(e2e)
+            e2e_stats = {"mean": round(sum(e2e) / len(e2e), 4), "cpu_baseline_median": round(statistics.median(e2e_rep), 4),
+                         "cpu_baseline_mean": round(sum(e2e_rep) / len(e2e_rep), 4)}
+            keep_rows = product_passes(B.BIN_PATH, args.warmup + args.steps, out_file, env, extra=["--keep-nvml-attached"])[args.warmup:]
+            keep_st, _ = stats(keep_rows)
+        finally:
+            if world > 1:
+                open(flag, "w").close()
+    elif world > 1:
+        t_wait = time.time()
+        while not os.path.exists(flag):
+            if time.time() - t_wait > 3600:
+                raise SystemExit("bench.py: rank 0 never finished the labeling passes")
+            time.sleep(0.05)
+
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    if world > 1:
+        os.environ.setdefault("GLOO_SOCKET_IFNAME", "lo")  # one node: loopback always exists, the hostname may not resolve
+        dist.init_process_group("gloo")  # host-side group: barriers; NCCL (below) only carries the result reduction
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+
     barrier()
+    if rank == 0 and world > 1:
+        try:
+            os.unlink(flag)
+        except OSError:
+            pass
+    node_gpus = node_gpu_count() if rank == 0 else None
+    cfg_line = workload_config(args.gpus, node_gpus, None) if rank == 0 else None  # asks nvidia-smi: after the timed host regions
 
     # ---- only now: CUDA, and NCCL for the result reduction ------------------------------------------------------------
     if not torch.cuda.is_available():

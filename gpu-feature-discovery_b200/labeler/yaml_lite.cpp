@@ -5,6 +5,7 @@
 #include <cmath>
 #include <cstdlib>
 #include <cstring>
+#include <map>
 
 namespace yamllite {
 
@@ -87,11 +88,37 @@ void append_utf8(std::string &o, uint32_t cp) {
     else { o += (char)(0xF0 | (cp >> 18)); o += (char)(0x80 | ((cp >> 12) & 0x3F)); o += (char)(0x80 | ((cp >> 6) & 0x3F)); o += (char)(0x80 | (cp & 0x3F)); }
 }
 
+using Anchors = std::map<std::string, Value>;
+
+// What a tag does to a SCALAR (yaml.v2 resolve(): an explicit core tag re-types the text; any other tag leaves a string).
+// `text` is the scalar's content (quotes already removed); collections keep their shape whatever the tag says.
+Value apply_scalar_tag(const std::string &tag, const std::string &text, Value v) {
+    if (tag.empty() || v.kind == Value::Array || v.kind == Value::Object) return v;
+    if (tag == "!!int" || tag == "!!float" || tag == "!!bool" || tag == "!!null") {
+        Value r = resolve_plain(text);
+        if (tag == "!!float" && r.kind == Value::Int) { r.kind = Value::Float; r.f = (double)r.i; }  // yaml.v2 resolve.go: int under !!float
+        return r;
+    }
+    if (tag == "!!binary") fail("unsupported YAML feature: !!binary");
+    Value out;  // !!str, !local, !<verbatim>: a string
+    out.kind = Value::String;
+    out.s = text;
+    out.quoted = true;
+    return out;
+}
+
 // ---- flow / JSON parser over a character range ----
 struct Flow {
     const std::string &t;
     size_t p;
-    explicit Flow(const std::string &text, size_t pos = 0) : t(text), p(pos) {}
+    Anchors *anchors;
+    explicit Flow(const std::string &text, size_t pos = 0, Anchors *a = nullptr) : t(text), p(pos), anchors(a) {}
+
+    std::string token() {  // an anchor / alias / tag name: up to a blank or a flow indicator
+        size_t s = p;
+        while (p < t.size() && !std::isspace((unsigned char)t[p]) && t[p] != ',' && t[p] != ']' && t[p] != '}' && t[p] != '[' && t[p] != '{') p++;
+        return t.substr(s, p - s);
+    }
 
     void ws() {
         while (p < t.size()) {
@@ -109,6 +136,7 @@ struct Flow {
             if (p >= t.size()) fail("unterminated double-quoted scalar");
             char c = t[p++];
             if (c == '"') break;
+            if (c == '\n') fail("unterminated quoted scalar on this line (scalars continued on a following line are not supported)");
             if (c != '\\') { o += c; continue; }
             if (p >= t.size()) fail("bad escape");
             char e = t[p++];
@@ -151,6 +179,7 @@ struct Flow {
                 if (p < t.size() && t[p] == '\'') { o += '\''; p++; continue; }
                 break;
             }
+            if (c == '\n') fail("unterminated quoted scalar on this line (scalars continued on a following line are not supported)");
             o += c;
         }
         return o;
@@ -159,6 +188,33 @@ struct Flow {
     Value value() {
         ws();
         if (p >= t.size()) fail("unexpected end of input");
+        if (t[p] == '*') {  // alias
+            p++;
+            std::string name = token();
+            if (!anchors || !anchors->count(name)) fail("unknown anchor '" + name + "' referenced");
+            return (*anchors)[name];
+        }
+        if (t[p] == '&' || t[p] == '!') {  // node properties, then the node
+            std::string anchor, tag;
+            while (p < t.size() && (t[p] == '&' || t[p] == '!')) {
+                bool is_anchor = t[p] == '&';
+                std::string tok = token();
+                if (is_anchor) anchor = tok.substr(1); else tag = tok;
+                ws();
+            }
+            Value v;
+            if (p < t.size() && t[p] != ',' && t[p] != ']' && t[p] != '}') {
+                size_t s = p;
+                v = value();
+                std::string text = v.quoted || v.kind == Value::String ? v.s : t.substr(s, p - s);
+                while (!text.empty() && std::isspace((unsigned char)text.back())) text.pop_back();
+                v = apply_scalar_tag(tag, text, v);
+            } else {
+                v = apply_scalar_tag(tag, "", v);
+            }
+            if (!anchor.empty() && anchors) (*anchors)[anchor] = v;
+            return v;
+        }
         char c = t[p];
         Value v;
         if (c == '{') {
@@ -169,6 +225,7 @@ struct Flow {
             while (true) {
                 ws();
                 std::string key;
+                bool key_quoted = true;
                 if (p < t.size() && t[p] == '"') key = dquoted();
                 else if (p < t.size() && t[p] == '\'') key = squoted();
                 else {
@@ -176,14 +233,30 @@ struct Flow {
                     while (p < t.size() && t[p] != ':' && t[p] != ',' && t[p] != '}' && t[p] != '\n') p++;
                     key = t.substr(s, p - s);
                     while (!key.empty() && std::isspace((unsigned char)key.back())) key.pop_back();
+                    key_quoted = false;
                 }
                 ws();
                 if (p >= t.size() || t[p] != ':') fail("expected ':' in flow mapping");
                 p++;
                 Value val = value();
-                bool dup = false;
-                for (auto &kv : v.obj) if (kv.first == key) { kv.second = val; dup = true; }
-                if (!dup) v.obj.emplace_back(key, val);
+                if (key == "<<" && !key_quoted) {  // merge key, applied where it stands (yaml.v2 decode.go:660-664)
+                    std::vector<const Value *> srcs;
+                    if (val.kind == Value::Object) srcs.push_back(&val);
+                    else if (val.kind == Value::Array) for (size_t i = val.arr.size(); i-- > 0;) srcs.push_back(&val.arr[i]);
+                    else fail("map merge requires map or sequence of maps as the value");
+                    for (const Value *src : srcs) {
+                        if (src->kind != Value::Object) fail("map merge requires map or sequence of maps as the value");
+                        for (const auto &m : src->obj) {
+                            bool dup = false;
+                            for (auto &kv : v.obj) if (kv.first == m.first) { kv.second = m.second; dup = true; }
+                            if (!dup) v.obj.emplace_back(m.first, m.second);
+                        }
+                    }
+                } else {
+                    bool dup = false;
+                    for (auto &kv : v.obj) if (kv.first == key) { kv.second = val; dup = true; }
+                    if (!dup) v.obj.emplace_back(key, val);
+                }
                 ws();
                 if (p < t.size() && t[p] == ',') { p++; ws(); if (p < t.size() && t[p] == '}') { p++; break; } continue; }
                 if (p < t.size() && t[p] == '}') { p++; break; }
@@ -219,10 +292,12 @@ struct Flow {
     }
 };
 
+
 // ---- block parser ----
 struct Line {
     int indent;
     std::string text;  // without indentation, comments and trailing blanks
+    size_t raw;        // index of this line in Block::raw (block scalars read the untouched text)
 };
 
 // strip a trailing comment that is outside quotes
@@ -239,35 +314,72 @@ std::string strip_comment(const std::string &s) {
     return s;
 }
 
+void ltrim(std::string &t) {
+    size_t b = 0;
+    while (b < t.size() && (t[b] == ' ' || t[b] == '\t')) b++;
+    t = t.substr(b);
+}
+
+struct Props {
+    std::string anchor, tag;
+};
+
+// "&a !!str rest" -> anchor "a", tag "!!str", t = "rest"
+void take_props(std::string &t, Props *p) {
+    while (!t.empty() && (t[0] == '&' || t[0] == '!')) {
+        size_t e = t.find_first_of(" \t");
+        std::string tok = t.substr(0, e);
+        if (t[0] == '&') {
+            if (tok.size() < 2) fail("anchor without a name");
+            p->anchor = tok.substr(1);
+        } else {
+            p->tag = tok;
+        }
+        t = e == std::string::npos ? "" : t.substr(e);
+        ltrim(t);
+    }
+}
+
 struct Block {
     std::vector<Line> lines;
+    std::vector<std::string> raw;  // every physical line of the first document, untouched
     size_t pos = 0;
+    Anchors anchors;
 
-    Value scalar_or_flow(const std::string &text) {
-        if (text.empty()) return Value();
+    bool is_dash(const std::string &t) const { return t == "-" || t.compare(0, 2, "- ") == 0; }
+
+    Value scalar_or_flow(const std::string &text, const std::string &tag) {
+        if (text.empty()) return apply_scalar_tag(tag, "", Value());
         char c = text[0];
-        if (c == '&' || c == '*' || c == '!' || c == '|' || c == '>') fail("unsupported YAML feature: " + text);
-        Flow f(text);
+        if (c == '*') {
+            std::string name = text.substr(1);
+            if (!anchors.count(name)) fail("unknown anchor '" + name + "' referenced");
+            return anchors[name];
+        }
+        if (c == '|' || c == '>') fail("block scalar not allowed here: " + text);
+        Flow f(text, 0, &anchors);
         if (c == '[' || c == '{' || c == '"' || c == '\'') {
             Value v = f.value();
             f.ws();
             if (f.p != text.size()) fail("trailing characters after value: " + text);
-            return v;
+            return apply_scalar_tag(tag, v.s, v);
         }
-        return resolve_plain(text);
+        return apply_scalar_tag(tag, text, resolve_plain(text));
     }
 
     // find "key:" split honoring quotes; returns false if the line is not a mapping entry
-    static bool split_key(const std::string &t, std::string *key, std::string *rest) {
+    static bool split_key(const std::string &t, std::string *key, std::string *rest, bool *quoted = nullptr) {
         size_t i = 0;
+        if (quoted) *quoted = false;
         if (!t.empty() && (t[0] == '"' || t[0] == '\'')) {
             Flow f(t);
             *key = t[0] == '"' ? f.dquoted() : f.squoted();
+            if (quoted) *quoted = true;
             i = f.p;
             while (i < t.size() && t[i] == ' ') i++;
             if (i >= t.size() || t[i] != ':') return false;
         } else {
-            if (!t.empty() && (t[0] == '[' || t[0] == '{')) return false;
+            if (!t.empty() && (t[0] == '[' || t[0] == '{' || t[0] == '&' || t[0] == '*' || t[0] == '!' || t[0] == '|' || t[0] == '>')) return false;
             for (; i < t.size(); i++)
                 if (t[i] == ':' && (i + 1 == t.size() || t[i + 1] == ' ' || t[i + 1] == '\t')) break;
             if (i >= t.size()) return false;
@@ -275,51 +387,151 @@ struct Block {
             while (!key->empty() && std::isspace((unsigned char)key->back())) key->pop_back();
         }
         *rest = t.substr(i + 1);
-        size_t b = 0;
-        while (b < rest->size() && (rest->at(b) == ' ' || rest->at(b) == '\t')) b++;
-        *rest = rest->substr(b);
+        ltrim(*rest);
         return true;
+    }
+
+    // Literal ('|') / folded ('>') block scalar whose header sits on line `head` (a Line index); the content is every following
+    // physical line that is blank or indented deeper than `parent_indent`.  Advances pos past the content.
+    Value block_scalar(const std::string &header, size_t head, int parent_indent) {
+        const bool folded = header[0] == '>';
+        int explicit_indent = 0;
+        char chomp = 0;  // 0 clip, '-' strip, '+' keep
+        for (size_t i = 1; i < header.size(); i++) {
+            char c = header[i];
+            if (c == '-' || c == '+') chomp = c;
+            else if (c >= '1' && c <= '9') explicit_indent = c - '0';
+            else fail("bad block scalar header: " + header);
+        }
+        size_t r = lines[head].raw + 1;
+        std::vector<std::string> body;
+        int content_indent = explicit_indent ? (parent_indent < 0 ? 0 : parent_indent) + explicit_indent : -1;
+        for (; r < raw.size(); r++) {
+            const std::string &ln = raw[r];
+            size_t ind = 0;
+            while (ind < ln.size() && ln[ind] == ' ') ind++;
+            bool blank = ind == ln.size();
+            if (!blank && (int)ind <= parent_indent) break;
+            if (content_indent < 0 && !blank) content_indent = (int)ind;
+            if (!blank && content_indent >= 0 && (int)ind < content_indent) break;
+            body.push_back(blank ? (content_indent >= 0 && (int)ln.size() > content_indent ? ln.substr((size_t)content_indent) : "")
+                                 : ln.substr((size_t)content_indent));
+        }
+        while (pos < lines.size() && lines[pos].raw < r) pos++;
+        // trailing blank lines belong to the chomping decision
+        size_t n = body.size();
+        while (n > 0 && body[n - 1].empty()) n--;
+        std::string out;
+        if (!folded) {
+            for (size_t i = 0; i < n; i++) { out += body[i]; if (i + 1 < n) out += '\n'; }
+        } else {
+            // folding: a single line break between two non-indented text lines becomes a space; blank lines give newlines;
+            // "more indented" lines (and the breaks around them) are kept literally
+            bool prev_more = false, prev_text = false;
+            size_t pending_blank = 0;
+            for (size_t i = 0; i < n; i++) {
+                const std::string &ln = body[i];
+                if (ln.empty()) { pending_blank++; continue; }
+                bool more = ln[0] == ' ' || ln[0] == '\t';
+                if (prev_text) {
+                    if (pending_blank) out.append(pending_blank + ((prev_more || more) ? 1 : 0), '\n');
+                    else out += (prev_more || more) ? '\n' : ' ';
+                } else {
+                    out.append(pending_blank, '\n');
+                }
+                pending_blank = 0;
+                out += ln;
+                prev_more = more;
+                prev_text = true;
+            }
+        }
+        if (n > 0 || chomp == '+') {
+            if (chomp == 0 && n > 0) out += '\n';
+            else if (chomp == '+') out.append((n > 0 ? 1 : 0) + (body.size() - n), '\n');
+        }
+        Value v;
+        v.kind = Value::String;
+        v.s = out;
+        v.quoted = true;
+        return v;
+    }
+
+    // the value that follows "key:" or "- " on the same line (`rest`), or the nested block when rest carries nothing but
+    // properties; `indent` is the indentation of the line the key / dash sits on, `head` its index in `lines` (pos is already past it)
+    Value value_after(std::string rest, int indent, size_t head, bool allow_same_indent_seq) {
+        Props props;
+        take_props(rest, &props);
+        Value v;
+        if (!rest.empty() && (rest[0] == '|' || rest[0] == '>')) {
+            v = apply_scalar_tag(props.tag, "", Value());
+            Value bs = block_scalar(rest, head, indent);
+            v = props.tag.empty() ? bs : apply_scalar_tag(props.tag, bs.s, bs);
+        } else if (!rest.empty()) {
+            v = scalar_or_flow(rest, props.tag);
+        } else if (pos < lines.size() &&
+                   (lines[pos].indent > indent || (allow_same_indent_seq && lines[pos].indent == indent && is_dash(lines[pos].text)))) {
+            v = parse_node(lines[pos].indent);
+        } else {
+            v = apply_scalar_tag(props.tag, "", Value());
+        }
+        if (!props.anchor.empty()) anchors[props.anchor] = v;
+        return v;
     }
 
     Value parse_node(int indent) {
         if (pos >= lines.size()) return Value();
         const Line &l = lines[pos];
-        if (l.text == "-" || l.text.compare(0, 2, "- ") == 0) return parse_seq(l.indent);
+        if (is_dash(l.text)) return parse_seq(l.indent);
         std::string k, r;
         if (split_key(l.text, &k, &r)) return parse_map(l.indent);
-        (void)indent;
-        Value v = scalar_or_flow(l.text);
+        // a scalar / flow collection / alias / block scalar standing alone on its line (document root or a sequence item's body)
+        size_t head = pos;
+        std::string text = l.text;
         pos++;
-        return v;
+        return value_after(text, indent - 1, head, false);
     }
 
     Value parse_seq(int indent) {
         Value v;
         v.kind = Value::Array;
-        while (pos < lines.size() && lines[pos].indent == indent &&
-               (lines[pos].text == "-" || lines[pos].text.compare(0, 2, "- ") == 0)) {
+        while (pos < lines.size() && lines[pos].indent == indent && is_dash(lines[pos].text)) {
             std::string rest = lines[pos].text.size() > 1 ? lines[pos].text.substr(2) : "";
             size_t lead = 0;
             while (lead < rest.size() && rest[lead] == ' ') lead++;
             rest = rest.substr(lead);
-            if (rest.empty()) {
-                pos++;
-                if (pos < lines.size() && lines[pos].indent > indent) v.arr.push_back(parse_node(lines[pos].indent));
-                else v.arr.push_back(Value());
-                continue;
-            }
             std::string k, r;
-            if (rest == "-" || rest.compare(0, 2, "- ") == 0 || split_key(rest, &k, &r)) {
+            if (!rest.empty() && (is_dash(rest) || split_key(rest, &k, &r))) {
                 // nested collection starting on the dash line: re-home the remainder as a virtual line
                 lines[pos].indent = indent + 2 + (int)lead;
                 lines[pos].text = rest;
                 v.arr.push_back(parse_node(lines[pos].indent));
                 continue;
             }
-            v.arr.push_back(scalar_or_flow(rest));
+            size_t head = pos;
             pos++;
+            v.arr.push_back(value_after(rest, indent, head, false));
         }
         return v;
+    }
+
+    static void map_put(Value &m, const std::string &key, const Value &val) {
+        for (auto &kv : m.obj)
+            if (kv.first == key) { kv.second = val; return; }
+        m.obj.emplace_back(key, val);
+    }
+    // "<<": yaml.v2 applies a merge WHERE IT STANDS in the mapping (decode.go:660-664): it overwrites keys set before it and is
+    // overwritten by keys after it; in a sequence of maps earlier entries win (decode.go:795-807).
+    static void map_merge(Value &m, const Value &src) {
+        if (src.kind == Value::Object) {
+            for (const auto &kv : src.obj) map_put(m, kv.first, kv.second);
+        } else if (src.kind == Value::Array) {
+            for (size_t i = src.arr.size(); i-- > 0;) {
+                if (src.arr[i].kind != Value::Object) fail("map merge requires map or sequence of maps as the value");
+                for (const auto &kv : src.arr[i].obj) map_put(m, kv.first, kv.second);
+            }
+        } else {
+            fail("map merge requires map or sequence of maps as the value");
+        }
     }
 
     Value parse_map(int indent) {
@@ -327,20 +539,14 @@ struct Block {
         v.kind = Value::Object;
         while (pos < lines.size() && lines[pos].indent == indent) {
             std::string key, rest;
-            if (lines[pos].text == "-" || lines[pos].text.compare(0, 2, "- ") == 0) break;
-            if (!split_key(lines[pos].text, &key, &rest)) fail("expected 'key: value' at: " + lines[pos].text);
+            bool quoted = false;
+            if (is_dash(lines[pos].text)) break;
+            if (!split_key(lines[pos].text, &key, &rest, &quoted)) fail("expected 'key: value' at: " + lines[pos].text);
+            size_t head = pos;
             pos++;
-            Value val;
-            if (!rest.empty()) {
-                val = scalar_or_flow(rest);
-            } else if (pos < lines.size() &&
-                       (lines[pos].indent > indent ||
-                        (lines[pos].indent == indent && (lines[pos].text == "-" || lines[pos].text.compare(0, 2, "- ") == 0)))) {
-                val = parse_node(lines[pos].indent);
-            }
-            bool dup = false;
-            for (auto &kv : v.obj) if (kv.first == key) { kv.second = val; dup = true; }
-            if (!dup) v.obj.emplace_back(key, val);
+            Value val = value_after(rest, indent, head, true);
+            if (key == "<<" && !quoted) map_merge(v, val);
+            else map_put(v, key, val);
         }
         if (pos < lines.size() && lines[pos].indent > indent) fail("bad indentation at: " + lines[pos].text);
         return v;
@@ -354,30 +560,38 @@ Value parse(const std::string &text) {
     size_t first = 0;
     while (first < text.size() && std::isspace((unsigned char)text[first])) first++;
     if (first < text.size() && (text[first] == '{' || text[first] == '[')) {
-        Flow f(text, first);
+        Anchors anchors;
+        Flow f(text, first, &anchors);
         Value v = f.value();
         f.ws();
         if (f.p != text.size()) fail("trailing characters after document");
         return v;
     }
+    // Only the FIRST document is read, as yaml.v2's Unmarshal does; directives (%YAML, %TAG) in front of it are skipped.
     Block b;
     size_t i = 0;
+    bool started = false;
     while (i <= text.size()) {
         size_t e = text.find('\n', i);
         if (e == std::string::npos) e = text.size();
-        std::string raw = text.substr(i, e - i);
+        std::string rawline = text.substr(i, e - i);
         i = e + 1;
-        if (!raw.empty() && raw.back() == '\r') raw.pop_back();
-        std::string s = strip_comment(raw);
+        if (!rawline.empty() && rawline.back() == '\r') rawline.pop_back();
+        if (rawline == "..." || rawline.compare(0, 4, "... ") == 0) { if (started) break; if (e == text.size()) break; continue; }
+        if (rawline == "---" || rawline.compare(0, 4, "--- ") == 0) {
+            if (started) break;  // a second document: not ours
+            started = true;
+            rawline = rawline.size() > 4 ? "    " + rawline.substr(4) : "";  // "--- value" keeps its value, at a column of its own
+        }
+        if (!started && !rawline.empty() && rawline[0] == '%') { if (e == text.size()) break; continue; }
+        b.raw.push_back(rawline);
+        std::string s = strip_comment(rawline);
         while (!s.empty() && (s.back() == ' ' || s.back() == '\t')) s.pop_back();
         size_t ind = 0;
         while (ind < s.size() && s[ind] == ' ') ind++;
         if (ind < s.size() && s[ind] == '\t') fail("tabs are not allowed for indentation");
         std::string body = s.substr(ind);
-        if (body.empty()) { if (e == text.size()) break; continue; }
-        if (body == "---") { if (!b.lines.empty()) fail("multiple documents are not supported"); continue; }
-        if (body == "...") break;
-        b.lines.push_back({(int)ind, body});
+        if (!body.empty()) { b.lines.push_back({(int)ind, body, b.raw.size() - 1}); started = true; }
         if (e == text.size()) break;
     }
     if (b.lines.empty()) return Value();

@@ -3,8 +3,11 @@
 // The reference reads its config file with sigs.k8s.io/yaml (YAML -> JSON -> encoding/json,
 // V/spec/config.go:74-99).  This reader covers what such config files use: block mappings and sequences,
 // flow sequences/mappings (so any JSON document parses), single/double-quoted and plain scalars, comments,
-// and YAML 1.1 scalar resolution as yaml.v2 does it (null/bool/int/float/string).  Anchors, tags, multi-line
-// scalars and multiple documents are not supported and raise a parse error.
+// YAML 1.1 scalar resolution as yaml.v2 does it (null/bool/int/float/string), anchors / aliases / merge keys ("<<", applied
+// where they stand, as yaml.v2 does), core and local tags on scalars, literal and folded block scalars with chomping and
+// indentation indicators, directives, and "first document only" for multi-document files (yaml.v2's Unmarshal).
+// Still refused with a parse error: plain / quoted scalars and flow collections that continue on a following line, complex
+// keys ("? "), properties in front of an implicit key ("&a key: v"), !!binary, tab indentation.
 #pragma once
 #include <cstdint>
 #include <stdexcept>
