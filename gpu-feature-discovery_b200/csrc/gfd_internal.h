@@ -95,6 +95,8 @@ struct gfd_mgr {
     bool attached = false;  // KEEP_ATTACHED: an extra nvmlInit reference is held
     gfd::NvmlApi nv;
     gfd::Cached<std::vector<std::unique_ptr<gfd_dev>>> devices;
+    gfd::Cached<std::string> driver_version;  // nvmlSystemGetDriverVersion, once per bracket
+    gfd::Cached<int> cuda_version;            // nvmlSystemGetCudaDriverVersion (NVML dlopens libcuda for it: ~0.4 ms)
     // Device objects of the previous bracket.  A handle used after gfd_shutdown is a caller bug, but it must get
     // GFD_ERR_NOT_INITIALIZED (what NVML answers for a stale handle), not a use-after-free: the objects stay
     // allocated until the next gfd_init or gfd_mgr_free.

@@ -310,6 +310,27 @@ int enumerate(gfd_mgr *m) {
     return m->devices.rc = 0;
 }
 
+// The two node-level queries; status and value cached per bracket like every per-device answer.
+int q_driver_version(gfd_mgr *m) {
+    if (m->driver_version.done) return m->driver_version.rc;
+    char v[NVML_SYSTEM_DRIVER_VERSION_BUFFER_SIZE];
+    memset(v, 0, sizeof v);
+    int rc = NVCALL(m, SystemGetDriverVersion, v, (unsigned)sizeof v);
+    if (rc == 0) m->driver_version.v = std::string(v, clen(v, sizeof v));
+    m->driver_version.rc = rc;
+    m->driver_version.done = true;
+    return rc;
+}
+int q_cuda_version(gfd_mgr *m) {
+    if (m->cuda_version.done) return m->cuda_version.rc;
+    int v = 0;
+    int rc = NVCALL(m, SystemGetCudaDriverVersion, &v);
+    m->cuda_version.v = v;
+    m->cuda_version.rc = rc;
+    m->cuda_version.done = true;
+    return rc;
+}
+
 void prefetch_one(gfd_dev *d) {
     q_mem(d);
     q_cc(d);
@@ -410,6 +431,8 @@ GFD_API int gfd_init(gfd_mgr *m) {
     m->nvml_calls = 0;
     m->dl_probes = 0;
     m->devices = {};
+    m->driver_version = {};
+    m->cuda_version = {};
     m->retired.clear();
     if (m->backend == GFD_BACKEND_NULL) { m->initialized = true; return 0; }  // null.go:35-37
     if (m->backend == GFD_BACKEND_CUDA) {
@@ -463,11 +486,9 @@ GFD_API int gfd_driver_version(gfd_mgr *m, char *buf, size_t len) {
     CHECK_MGR(m);
     if (m->backend == GFD_BACKEND_NULL) return GFD_ERR_UNSUPPORTED_BACKEND;
     if (m->backend == GFD_BACKEND_CUDA) return copy_out("unknown.unknown.unknown", buf, len);  // cuda-lib.go:66-68
-    char v[NVML_SYSTEM_DRIVER_VERSION_BUFFER_SIZE];
-    memset(v, 0, sizeof v);
-    int rc = NVCALL(m, SystemGetDriverVersion, v, (unsigned)sizeof v);
+    int rc = q_driver_version(m);
     if (rc) return rc;
-    return copy_out(std::string(v, clen(v, sizeof v)), buf, len);
+    return copy_out(m->driver_version.v, buf, len);
 }
 
 GFD_API int gfd_cuda_driver_version(gfd_mgr *m, unsigned *major, unsigned *minor) {
@@ -475,9 +496,9 @@ GFD_API int gfd_cuda_driver_version(gfd_mgr *m, unsigned *major, unsigned *minor
     if (!major || !minor) return GFD_ERR_BAD_ARGUMENT;
     if (m->backend == GFD_BACKEND_NULL) return GFD_ERR_UNSUPPORTED_BACKEND;
     if (m->backend == GFD_BACKEND_CUDA) return cuda_mgr_driver_version(m, major, minor);
-    int v = 0;
-    int rc = NVCALL(m, SystemGetCudaDriverVersion, &v);
+    int rc = q_cuda_version(m);
     if (rc) return rc;
+    const int v = m->cuda_version.v;
     // nvml-lib.go:47-48 converts the Go int (64-bit) straight to uint
     *major = (unsigned)(uint64_t)((int64_t)v / 1000);
     *minor = (unsigned)(uint64_t)((int64_t)v % 1000 / 10);
@@ -513,6 +534,13 @@ GFD_API int gfd_prefetch(gfd_mgr *m, int threads) {
     }
     std::atomic<size_t> next{0};
     std::vector<std::thread> pool;
+    // The node-level queries run beside the device walk on a thread of their own: nvmlSystemGetCudaDriverVersion makes NVML
+    // dlopen libcuda (~0.4 ms) and nothing it needs waits for a GPU attach.  Joined on every path out of this function.
+    struct SystemQueries {
+        std::thread t;
+        explicit SystemQueries(gfd_mgr *m) : t([m] { q_driver_version(m); q_cuda_version(m); }) {}
+        ~SystemQueries() { if (t.joinable()) t.join(); }
+    } system_queries(m);
     if (!m->devices.done) {
         // Threaded walk.  nvmlDeviceGetHandleByIndex is where the driver attaches a GPU (~8 ms each on B200, measured
         // in profiles/r1_nvml_phase_timing.txt), so on a multi-GPU node the attach itself is what gets spread over
@@ -521,7 +549,12 @@ GFD_API int gfd_prefetch(gfd_mgr *m, int threads) {
         unsigned count = 0;
         int rc = NVCALL(m, DeviceGetCount, &count);
         count = bench_device_cap(count);
-        if (rc == 0 && count < 2) return 0;  // nothing to spread: leave the (serial) walk to gfd_device_count
+        if (rc == 0 && count < 2) {  // nothing to spread across GPUs: walk here, beside the system-queries thread
+            m->devices.done = false;
+            if (enumerate(m) == 0)
+                for (auto &d : m->devices.v) prefetch_one(d.get());
+            return 0;
+        }
         m->devices.done = true;
         if (rc) { m->devices.rc = rc; return 0; }  // reported by gfd_device_count, where the reference would see it
         std::vector<std::unique_ptr<gfd_dev>> slots(count);

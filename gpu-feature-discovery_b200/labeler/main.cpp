@@ -9,6 +9,8 @@
 #include <cstring>
 #include <ctime>
 #include <string>
+#include <thread>
+#include <exception>
 
 #include <unistd.h>
 
@@ -61,13 +63,29 @@ bool run(gfdlm::Manager &mgr, const gfdcfg::Config &config, const sigset_t &sigs
     while (true) {
         double t0 = now_ms();
         gfdlm::PhaseTimes ph;
+        // The vGPU scan (sysfs reads, no NVML) has no input from the NVML bracket, so it runs beside it on a thread of its own;
+        // its result -- or its error -- is looked at only where the reference would get to it (the lazy part of
+        // labelers.Labels(), after the NVML labeler has been built: main.go:160-172), so an NVML failure still wins.
+        gfdlm::Labels vgpu;
+        std::exception_ptr vgpu_error;
+        std::thread vgpu_thread([&] {
+            try {
+                vgpu = gfdlm::vgpu_labels(config);
+            } catch (...) {
+                vgpu_error = std::current_exception();
+            }
+        });
+        struct Join {
+            std::thread &t;
+            ~Join() { if (t.joinable()) t.join(); }
+        } join{vgpu_thread};
         gfdlm::Labels nvml = gfdlm::nvml_labels(mgr, config, &ph);  // lm.NewLabelers: the eager NVML part
         double t1 = now_ms();
         gfdlm::Labels labels = timestamp;                      // lm.Merge(timestampLabeler, loopLabelers): later wins
         for (auto &kv : nvml) labels[kv.first] = kv.second;
-        gfdlm::Labels vgpu;
+        vgpu_thread.join();
         try {
-            vgpu = gfdlm::vgpu_labels(config);                 // the lazy part: sysfs is read after the NVML bracket
+            if (vgpu_error) std::rethrow_exception(vgpu_error);
         } catch (const gfdlm::PassError &e) {
             throw gfdlm::PassError(std::string("error generating labels: error generating labels: ") + e.what());
         }
