@@ -420,10 +420,23 @@ def main():
     dev = torch.device("cuda", local_rank)
     nccl = None
     if world > 1:
+        # NCCL prints its version banner on stdout when the first communicator comes up; stdout carries exactly one JSON
+        # line, so file descriptor 1 points at stderr while the group is created and warmed.
+        sys.stdout.flush()
+        saved_stdout = os.dup(1)
+        os.dup2(2, 1)
         try:
-            nccl = dist.new_group(backend="nccl", device_id=dev)
-        except TypeError:  # older signature
-            nccl = dist.new_group(backend="nccl")
+            try:
+                nccl = dist.new_group(backend="nccl", device_id=dev)
+            except TypeError:  # older signature
+                nccl = dist.new_group(backend="nccl")
+            warm = torch.zeros(1, device=dev)
+            dist.all_reduce(warm, group=nccl)
+            torch.cuda.synchronize()
+        finally:
+            sys.stdout.flush()
+            os.dup2(saved_stdout, 1)
+            os.close(saved_stdout)
 
     def gpu_barrier():
         torch.cuda.synchronize()
