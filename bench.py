@@ -299,18 +299,23 @@ def p2p_section(B, n, bytes_per_direction=1 << 30, warmup=2, iters=10):
     return IS verified = true.  -> (roofline_p2p object, kernel launches made)."""
     out, launches = {}, 0
     m_even = n if n % 2 == 0 else n + 1
-    for mode, name in ((B.PROBE_READ, "read"), (B.PROBE_PUSH, "push")):
+    active = n if n % 2 == 0 else n - 1
+    for mode, name in ((B.PROBE_READ, "read"), (B.PROBE_PUSH, "push"), (B.PROBE_DMA, "dma")):
         m, ring = B.probe_p2p_matrix(n, bytes_per_direction, warmup=warmup, iters=iters, mode=mode)
         off = [m[a][b] for a in range(n) for b in range(n) if a != b]
         out[name] = {"bound": "nvlink", "achieved_per_direction_min": round(min(off), 1), "achieved_per_direction_max": round(max(off), 1),
                      "achieved_ring_aggregate": round(ring, 1), "peak": 900.0, "unit": "GB/s", "frac": round(min(off) / 900.0, 4),
                      "mode": name, "pairs": n * (n - 1), "verified": True, "bytes_per_direction_per_launch": bytes_per_direction,
                      "iters": iters, "schedule": "%d rounds x %d disjoint pairs, both directions at once; then an all-GPU ring" % (m_even - 1, n // 2)}
-        per_round = (n if n % 2 == 0 else n - 1) * (warmup + iters)
-        verify = (n if n % 2 == 0 else n - 1) if mode != B.PROBE_READ else 0
-        launches += 2 * n + (m_even - 1) * (per_round + verify) + n * (warmup + iters) + (n if mode != B.PROBE_READ else 0)
+        moved_by_our_kernels = mode != B.PROBE_DMA  # DMA = cudaMemcpyAsync between peers (copy engine): the yardstick, not a kernel of ours
+        timed = ((m_even - 1) * active + n) * (warmup + iters) if moved_by_our_kernels else 0
+        verify = ((m_even - 1) * active + n) if mode != B.PROBE_READ else 0  # the destination is re-read by hbm_read_fold
+        launches += 2 * n + timed + verify
+        if not moved_by_our_kernels:
+            out[name]["note"] = "copy engine (cudaMemcpyAsync between peers), same schedule and verification: what the links give to DMA, for comparison"
     top = dict(out["read"])
     top["push"] = out["push"]
+    top["dma"] = out["dma"]
     top["verified"] = out["read"]["verified"] and out["push"]["verified"]
     top["peak_source"] = "NVLink 5 nominal, 900 GB/s per direction per GPU (B200_PROFILING.md); kernels: hbm_read_fold_kernel<peer>, hbm_copy_kernel"
     return top, launches
@@ -355,7 +360,13 @@ def main():
     # imported torch, has asked nvidia-smi nothing, holds no CUDA context; the other ranks sleep on a flag file (no torch
     # import, no process group, no context) -- an NCCL barrier would spin a kernel on the very GPUs the pass attaches to
     # (2 GPUs: pass median 50 ms with the other rank parked in one, 21-30 ms without).
-    flag = os.path.join(tempfile.gettempdir(), "gfd-bench-%d-%s.region-a-done" % (os.getppid(), os.environ.get("MASTER_PORT", "0")))
+    # the flag's name is unique per launch: under torchrun every worker has the same parent (the agent); other launchers fall
+    # back to address + port, where a left-over file of an earlier run is told apart by its age
+    t_start = time.time()
+    launch_id = str(os.getppid()) if "TORCHELASTIC_RUN_ID" in os.environ else os.environ.get("MASTER_ADDR", "local")
+    flag = os.path.join(tempfile.gettempdir(), "gfd-bench-%s-%s.region-a-done" % (launch_id, os.environ.get("MASTER_PORT", "0")))
+    if rank == 0 and world > 1 and os.path.exists(flag):
+        os.unlink(flag)
     pass_ms = e2e_ms = 0.0
     prod_st = prod_ph = rep_st = rep_ph = keep_st = None
     e2e_stats, rep_info, product_text, replay_text = {}, {}, "", ""
@@ -388,7 +399,7 @@ def main():
                 open(flag, "w").close()
     elif world > 1:
         t_wait = time.time()
-        while not os.path.exists(flag):
+        while not (os.path.exists(flag) and os.path.getmtime(flag) >= t_start - 1.0):
             if time.time() - t_wait > 3600:
                 raise SystemExit("bench.py: rank 0 never finished the labeling passes")
             time.sleep(0.05)

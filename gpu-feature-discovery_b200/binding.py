@@ -29,7 +29,7 @@ GFD_ERR_SHIM = 200000
 BACKEND_NVML, BACKEND_CUDA, BACKEND_NULL = 0, 1, 2
 MGR_KEEP_ATTACHED = 1
 MGR_CURRENT_TABLES = 2
-PROBE_READ, PROBE_COPY, PROBE_PUSH, PROBE_WRITE = 0, 1, 2, 3
+PROBE_READ, PROBE_COPY, PROBE_PUSH, PROBE_WRITE, PROBE_DMA = 0, 1, 2, 3, 4
 
 # every symbol include/gfd_b200.h declares (tests/test_cabi_symbols.py checks the header against this list)
 SYMBOLS = [

@@ -636,6 +636,10 @@ int time_kernel(int run_dev, void *dst, const void *src, size_t bytes, int warmu
     int grid = 0;
     auto once = [&]() -> int {
         if (mode == GFD_PROBE_WRITE) return launch_fill(run_dev, dst, bytes, seed, st.s, &grid);
+        if (mode == GFD_PROBE_DMA) {  // the copy engine, for comparison: no kernel of ours moves these bytes
+            CUDA_TRY(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToDevice, st.s));
+            return 0;
+        }
         if (mode == GFD_PROBE_COPY || mode == GFD_PROBE_PUSH) return launch_copy(run_dev, dst, src, bytes, st.s, &grid, src_is_peer);
         return launch_read(run_dev, src, bytes, static_cast<gfd_checksum *>(d_out.p), scratch.p, st.s, &grid, src_is_peer);
     };
@@ -703,7 +707,8 @@ GFD_API int gfd_probe_p2p(int src_device, int dst_device, size_t bytes, int warm
     int rc = device_count_checked(&n);
     if (rc) return rc;
     if (!out || src_device < 0 || dst_device < 0 || src_device >= n || dst_device >= n || src_device == dst_device ||
-        bytes == 0 || iters <= 0 || warmup < 0 || (mode != GFD_PROBE_READ && mode != GFD_PROBE_COPY && mode != GFD_PROBE_PUSH))
+        bytes == 0 || iters <= 0 || warmup < 0 ||
+        (mode != GFD_PROBE_READ && mode != GFD_PROBE_COPY && mode != GFD_PROBE_PUSH && mode != GFD_PROBE_DMA))
         return GFD_ERR_BAD_ARGUMENT;
     // pull modes run on the destination GPU and load from the source's memory; push runs on the source GPU and stores
     // into the destination's memory (posted writes: no request/response round trip on the link)
@@ -763,7 +768,10 @@ int p2p_launch(int run_dev, P2PDev &me, const void *peer_src, size_t bytes, int 
     int rc;
     if (timed) CUDA_TRY(cudaEventRecord(me.e0, me.st));
     for (int i = 0; i < reps; i++) {
-        if (mode == GFD_PROBE_COPY) rc = launch_copy(run_dev, me.dst, peer_src, bytes, me.st, nullptr, true);
+        if (mode == GFD_PROBE_DMA) {
+            CUDA_TRY(cudaMemcpyAsync(me.dst, peer_src, bytes, cudaMemcpyDeviceToDevice, me.st));
+            rc = 0;
+        } else if (mode == GFD_PROBE_COPY) rc = launch_copy(run_dev, me.dst, peer_src, bytes, me.st, nullptr, true);
         else if (mode == GFD_PROBE_PUSH) rc = launch_copy(run_dev, const_cast<void *>(peer_src), me.src, bytes, me.st, nullptr);  // peer_src = the partner's dst
         else rc = launch_read(run_dev, peer_src, bytes, static_cast<gfd_checksum *>(me.out), me.scratch, me.st, nullptr, true);
         if (rc) return rc;
@@ -787,7 +795,7 @@ GFD_API int gfd_probe_p2p_matrix(int n_devices, size_t bytes, int warmup, int it
     int rc = device_count_checked(&n);
     if (rc) return rc;
     if (!gbps_matrix || n_devices < 2 || n_devices > n || n_devices > kMaxDevices || bytes == 0 || iters <= 0 || warmup < 0 ||
-        (mode != GFD_PROBE_READ && mode != GFD_PROBE_COPY && mode != GFD_PROBE_PUSH))
+        (mode != GFD_PROBE_READ && mode != GFD_PROBE_COPY && mode != GFD_PROBE_PUSH && mode != GFD_PROBE_DMA))
         return GFD_ERR_BAD_ARGUMENT;
     const int N = n_devices;
     for (int i = 0; i < N * N; i++) gbps_matrix[i] = 0.0;

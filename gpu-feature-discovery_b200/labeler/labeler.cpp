@@ -613,6 +613,15 @@ Labels probe_labels(const gfdcfg::Config &config) {
             int wpairs = 0;
             double wmin = min_pair(&wpairs);
             if (wpairs) out["nvidia.com/gpu.probe.nvlink.p2p-write-gbps"] = std::to_string((long long)wmin);
+            // and what the copy engine gets over the same links under the same schedule (cudaMemcpy between peers: no kernel
+            // of ours) -- the figure a framework's peer copies will see, and the yardstick for the two kernel figures above
+            std::fill(m.begin(), m.end(), 0.0);
+            double ring_d = 0.0;
+            rc = probe_p2p_matrix(n, bytes, 2, 10, GFD_PROBE_DMA, m.data(), &ring_d);
+            if (rc) fail("NVLink copy-engine probe failed", rc);
+            int dpairs = 0;
+            double dmin = min_pair(&dpairs);
+            if (dpairs) out["nvidia.com/gpu.probe.nvlink.p2p-dma-gbps"] = std::to_string((long long)dmin);
         }
     }
     return out;

@@ -270,7 +270,9 @@ enum gfd_probe_mode {
     GFD_PROBE_READ = 0,
     GFD_PROBE_COPY = 1,
     GFD_PROBE_PUSH = 2, /* p2p only: the source GPU stores into the peer */
-    GFD_PROBE_WRITE = 3 /* hbm only: the fill kernel is what gets timed (bytes written / time) */
+    GFD_PROBE_WRITE = 3, /* hbm only: the fill kernel is what gets timed (bytes written / time) */
+    GFD_PROBE_DMA = 4   /* p2p only: the destination GPU's stream pulls with cudaMemcpyAsync (the copy engine, no kernel of this
+                           library) -- the link's own limit beside what SM-issued loads and stores get; verified like COPY */
 };
 typedef struct gfd_probe_result {
     double gbps;           /* algorithmic bytes (bytes, or 2*bytes for copy over HBM; bytes per direction for p2p) / time */

@@ -93,15 +93,17 @@ def test_p2p_section_shape_and_launch_count():
     import bench
 
     class FakeB:
-        PROBE_READ, PROBE_PUSH = 0, 2
+        PROBE_READ, PROBE_PUSH, PROBE_DMA = 0, 2, 4
 
         @staticmethod
         def probe_p2p_matrix(n, nbytes, warmup, iters, mode):
-            base = 670.0 if mode == 0 else 705.0
+            base = {0: 670.0, 2: 705.0, 4: 770.0}[mode]
             return [[0.0 if a == b else base + a + b for b in range(n)] for a in range(n)], base * n
     r, launches = bench.p2p_section(FakeB, 4, warmup=2, iters=10)
     assert r["bound"] == "nvlink" and r["peak"] == 900.0 and r["pairs"] == 12 and r["verified"] is True
     assert r["achieved_per_direction_min"] == 671.0 and r["push"]["achieved_per_direction_min"] == 706.0
     assert r["mode"] == "read" and r["push"]["mode"] == "push" and r["achieved_ring_aggregate"] == 2680.0
     # per mode: fill + pattern per GPU (8), 3 rounds x 4 GPUs x 12 launches (144), ring 4 x 12 (48); PUSH re-reads every destination
-    assert launches == (8 + 144 + 48) + (8 + 144 + 48 + 3 * 4 + 4)
+    # the copy-engine pass launches only the one-off fill / pattern kernels and the verifying re-reads
+    assert launches == (8 + 144 + 48) + (8 + 144 + 48 + 3 * 4 + 4) + (8 + 3 * 4 + 4)
+    assert r["dma"]["achieved_per_direction_min"] == 771.0 and "copy engine" in r["dma"]["note"]

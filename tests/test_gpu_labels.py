@@ -269,8 +269,10 @@ def test_probe_nvlink_adds_read_and_write_labels(B, tmp_path):
         assert extra == []
         return
     kv = dict(l.split("=") for l in extra)
-    assert sorted(kv) == ["nvidia.com/gpu.probe.nvlink.p2p-read-gbps", "nvidia.com/gpu.probe.nvlink.p2p-write-gbps",
-                          "nvidia.com/gpu.probe.nvlink.pairs", "nvidia.com/gpu.probe.nvlink.ring-gbps"]
+    assert sorted(kv) == ["nvidia.com/gpu.probe.nvlink.p2p-dma-gbps", "nvidia.com/gpu.probe.nvlink.p2p-read-gbps",
+                          "nvidia.com/gpu.probe.nvlink.p2p-write-gbps", "nvidia.com/gpu.probe.nvlink.pairs",
+                          "nvidia.com/gpu.probe.nvlink.ring-gbps"]
+    assert 50 < int(kv["nvidia.com/gpu.probe.nvlink.p2p-dma-gbps"]) < 2000
     assert int(kv["nvidia.com/gpu.probe.nvlink.pairs"]) == n * (n - 1)
     assert 50 < int(kv["nvidia.com/gpu.probe.nvlink.p2p-read-gbps"]) < 2000
     assert 50 < int(kv["nvidia.com/gpu.probe.nvlink.p2p-write-gbps"]) < 2000

@@ -276,6 +276,8 @@ def test_p2p_probe(env):
     assert 50 < c.gbps < 2000, c.gbps
     p = B.probe_p2p(1, 0, n, warmup=2, iters=5, mode=B.PROBE_PUSH)
     assert c.verified == 1 and p.verified == 1 and c.checksum.tuple() == p.checksum.tuple() == r.checksum.tuple()
+    d = B.probe_p2p(1, 0, n, warmup=2, iters=5, mode=B.PROBE_DMA)     # the copy engine over the same link, verified the same way
+    assert d.verified == 1 and d.checksum.tuple() == r.checksum.tuple() and 50 < d.gbps < 2000, d.gbps
 
 
 def test_p2p_matrix_concurrent_tournament(env):
@@ -292,6 +294,8 @@ def test_p2p_matrix_concurrent_tournament(env):
             else:
                 assert 50 < m[a][b] < 2000, (a, b, m[a][b])
     assert ring > 50 * n
+    md, ring_d = B.probe_p2p_matrix(n, 1 << 28, warmup=1, iters=5, mode=B.PROBE_DMA)
+    assert all(50 < md[a][b] < 2000 for a in range(n) for b in range(n) if a != b) and ring_d > 50 * n
 
 
 def test_random_sizes_and_offsets(env):
