@@ -14,7 +14,7 @@ import yaml
 from hypothesis import HealthCheck, given, settings, strategies as st
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-DUMP = os.path.join(ROOT, "tools", "yaml_dump")
+DUMP = os.environ.get("GFD_YAML_DUMP", os.path.join(ROOT, "tools", "yaml_dump"))  # GFD_YAML_DUMP=<ASan build> for sanitizer runs
 
 
 def product_parse(text):
@@ -192,3 +192,15 @@ def test_config_file_with_anchors_and_block_scalars_reaches_the_labeler(tmp_path
     assert rc == 0, se
     got = open(out).read()
     assert "nvidia.com/gpu.replicas=2\n" in got and "nvidia.com/gpu.product=NVIDIA-B200-SHARED\n" in got and "nvidia.com/mig.strategy=mixed\n" in got
+
+
+@settings(max_examples=500, deadline=None, suppress_health_check=[HealthCheck.too_slow])
+@given(text=st.text(alphabet="ab01 \n\t-:&*!|>'\"[]{},#%<?.~+_\\", min_size=0, max_size=60))
+def test_reader_never_crashes_or_hangs(text):
+    """Arbitrary YAML-looking input: a value or a clean parse error, never a signal, never a hang (a config file is user input)."""
+    p = subprocess.run([DUMP], input=text.encode(), capture_output=True, timeout=20)
+    assert p.returncode in (0, 1), (text, p.returncode, p.stderr[-300:])
+    if p.returncode == 1:
+        assert p.stderr.decode().startswith("yaml: "), p.stderr
+    else:
+        json.loads(p.stdout.decode())
