@@ -7,8 +7,9 @@
  *     device <total bytes> <cc major> <cc minor> <name ...>
  *     rc <symbol> <CUresult>              return-code override
  * cuDeviceTotalMem is the LEGACY unversioned entry point (the reference binds that name, not _v2): it writes
- * a 32-bit value.  What a real Tegra driver stores there for > 4 GiB is not known to us; the fake stores the low
- * 32 bits and the oracle models the same, so this path is "parity unpinned" (no hardware, no reference test).
+ * a 32-bit value, SATURATED at 0xFFFFFFFF for a device with more than 4 GiB -- observed on the real libcuda of a B200 box
+ * (driver 580.x: 4294967295 for a 191 502 876 672-byte device; tests/test_gpu_cuda_backend.py pins it).  The oracle models
+ * the same.  There is still no Tegra hardware and no reference test for this path.
  */
 #define _GNU_SOURCE
 #include <stdio.h>
@@ -64,7 +65,7 @@ EXPORT int cuDeviceTotalMem(unsigned int *bytes, int dev) {
     int r = rc("cuDeviceTotalMem");
     if (r) return r;
     if (dev < 0 || dev >= nd) return 101;
-    *bytes = (unsigned int)(D[dev].total & 0xFFFFFFFFull);
+    *bytes = D[dev].total > 0xFFFFFFFFull ? 0xFFFFFFFFu : (unsigned int)D[dev].total;
     return 0;
 }
 EXPORT int cuDeviceGetName(char *name, int len, int dev) {

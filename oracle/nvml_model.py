@@ -548,9 +548,10 @@ class RawCuda:
 
     def device_total_mem(self, d):
         # the reference binds the legacy unversioned cuDeviceTotalMem (32-bit out-parameter) into a zeroed uint64
-        # (internal/cuda/cuda.go:108, api.go:107-112): modelled as the low 32 bits.  Parity unpinned (no Tegra here).
+        # (internal/cuda/cuda.go:108, api.go:107-112).  The real driver SATURATES that value at 0xFFFFFFFF for devices above
+        # 4 GiB (measured through the same symbol on a B200 box, tests/test_gpu_cuda_backend.py); it does not wrap.
         r = self._rc("cuDeviceTotalMem")
-        return (r, None) if r else (0, self.devices[d][0] & 0xFFFFFFFF)
+        return (r, None) if r else (0, min(self.devices[d][0], 0xFFFFFFFF))
 
     def device_get_name(self, d):
         r = self._rc("cuDeviceGetName")

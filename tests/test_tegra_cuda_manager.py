@@ -1,7 +1,8 @@
 """The Tegra path: no NVML, /etc/nv_tegra_release present -> CUDA-driver manager (internal/resource/factory.go:59-70,
 cuda-lib.go, cuda-device.go, internal/cuda/*).  Product = gpu-feature-discovery over a fake libcuda.so.1; checker = the
 oracle's CudaManager over the same fixture.  (Parity for this path is unpinned: no reference test touches it and there
-is no Tegra hardware here -- see the fake's header for the one modelling assumption, the legacy cuDeviceTotalMem.)"""
+is no Tegra hardware here; the fake's one modelling choice, what the legacy cuDeviceTotalMem stores above 4 GiB, follows the
+real libcuda of a B200 box -- tests/test_gpu_cuda_backend.py.)"""
 import os
 
 import pytest
@@ -15,7 +16,7 @@ GIB = 1 << 30
 CASES = {
     "orin": M.RawCuda([(3 * GIB + 123456789, 8, 7, "Orin (nvgpu)")], version=12020),
     "xavier two devices": M.RawCuda([(2 * GIB, 7, 2, "Xavier"), (2 * GIB, 7, 2, "Xavier")], version=11040),
-    "memory above 4 GiB wraps in the legacy call": M.RawCuda([(61 * GIB + 5 * (1 << 20), 8, 7, "Orin (nvgpu)")], version=12060),
+    "memory above 4 GiB saturates in the legacy call": M.RawCuda([(61 * GIB + 5 * (1 << 20), 8, 7, "Orin (nvgpu)")], version=12060),
     "no devices": M.RawCuda([], version=12020),
     "init fails": M.RawCuda([(GIB, 8, 7, "Orin")], rc={"cuInit": 100}),
     "count fails": M.RawCuda([(GIB, 8, 7, "Orin")], rc={"cuDeviceGetCount": 3}),
