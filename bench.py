@@ -103,6 +103,7 @@ class ClockSampler(threading.Thread):
         return {"sm_mhz": statistics.median(sm), "sm_max_mhz": max(mx), "reasons": sorted(reasons), "samples": len(sm)}
 
 
+SETTLE_S = float(os.environ.get("GFD_BENCH_SETTLE_S", "5"))  # idle time before the first pass, both arms: a GPU that ran kernels in the last ~2 s answers NVML 2-3 ms faster
 CHUNK = 5  # timed passes per process in the interleaved series (each process adds one untimed pass of its own first)
 PHASE_KEYS = ("init", "attach", "labels", "shutdown")
 
@@ -228,6 +229,9 @@ def workload_config(gpus, node_gpus, gpus_labelled):
                           "of the node, so its share of the pass does not shrink with N)" % (gpus, node_gpus),
             "statistic": "value = MEDIAN of the K timed passes, ms_per_step = their mean; W warm-up passes untimed; passes run in "
                          "processes of %d timed passes (+1 untimed process warm-up pass each)" % CHUNK,
+            "settle_s": SETTLE_S,
+            "settle": "both arms idle for %.0f s before their first pass: whatever ran on the GPU just before (tests, the other arm's kernels) makes "
+                      "the next ~2 s of NVML attaches 2-3 ms cheaper (profiles/r2_gpu_state_decay_1xB200.txt)" % SETTLE_S,
             "probe": "opt-in hbm_read_fold, %d MiB per launch (input >> 126 MB L2, so no L2 flush between iterations)" % (PROBE_BYTES >> 20),
             "parallelism": "the pass is per node: rank 0 labels the first N GPUs (one host thread per GPU), no collective; probes are "
                            "per-GPU replicas; P2P = one kernel per directed pair, no NCCL",
@@ -244,6 +248,7 @@ def reference_arm(args, rank, world):
     out = os.path.join(tmp, "gfd")
     env = bench_env(args.gpus)
     last = {}
+    time.sleep(SETTLE_S)
 
     def run(n):
         rows, r = replay_passes(n, out, env)
@@ -375,6 +380,7 @@ def main():
             rows, r = replay_passes(n, replay_out, env)
             rep_info.update(r)
             return rows
+        time.sleep(SETTLE_S)
         try:
             prod_rows, rep_rows = series(args.warmup, args.steps, lambda n: product_passes(B.BIN_PATH, n, out_file, env), run_replay)
             prod_st, prod_ph = stats(prod_rows)
@@ -487,6 +493,25 @@ def main():
     kernel_ms = e0.elapsed_time(e1) / args.steps
     probe_gbps = PROBE_BYTES / (kernel_ms * 1e-3) / 1e9
     checksum = tuple(int(v) for v in d_out.cpu().numpy().view(np.uint64))
+    # the other two HBM kernels of the library, timed the same way (reported beside the dominant one, not instead of it)
+    other_kernels = []
+    dst = torch.empty(PROBE_BYTES, dtype=torch.uint8, device=dev)
+    for kname, algorithmic, call in (
+            ("hbm_copy_kernel", 2 * PROBE_BYTES, lambda: B.hbm_copy(dst.data_ptr(), buf.data_ptr(), PROBE_BYTES, stream.cuda_stream)),
+            ("fill_pattern_kernel", PROBE_BYTES, lambda: B.hbm_fill_pattern(dst.data_ptr(), PROBE_BYTES, 1, stream.cuda_stream))):
+        for _ in range(args.warmup):
+            call()
+        k0, k1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        k0.record(stream)
+        for _ in range(args.steps):
+            call()
+        k1.record(stream)
+        torch.cuda.synchronize()
+        launches += args.warmup + args.steps
+        ms = k0.elapsed_time(k1) / args.steps
+        other_kernels.append({"kernel": kname, "bound": "hbm", "algorithmic_bytes_per_launch": algorithmic, "ms_per_launch": round(ms, 5),
+                              "achieved": round(algorithmic / (ms * 1e-3) / 1e9, 1), "unit": "GB/s"})
+    del dst
     sampler.stop()
     clocks = sampler.summary()
 
@@ -580,6 +605,7 @@ def main():
                      "kernel": "hbm_read_fold_kernel (one launch per checksum; the last CTA folds the partials)",
                      "algorithmic_bytes_per_launch": PROBE_BYTES, "ms_per_launch": round(kernel_ms, 5),
                      "frac_of_nominal_7700": round(probe_gbps / 7700.0, 4)},
+        "roofline_other_kernels": [dict(k, peak=peak, frac=round(k["achieved"] / peak, 4)) for k in other_kernels],
         "cpu_baseline": {"value": rep_st["median"], "unit": "ms", "cores": 1, "kind": "port",
                          "sample": "%d passes of oracle/ref_replay (C replay of the reference's NVML call sequence: %d NVML calls + %d dlopen "
                                    "cycles per pass) INTERLEAVED with the product's passes, chunks of %d, same device cap"

@@ -45,7 +45,8 @@ def test_reduce_over_ranks_gloo_world2():
 def test_reference_arm_runs_on_rank0_only(tmp_path):
     """`bench.py --impl reference` under torchrun: rank 0 prints the line, every other rank exits 0 without work."""
     fix = use_node(N.nodes()["c3_8xB200"], tmp_path)
-    env = dict(os.environ, GFD_FAKE_NVML=fix, LD_LIBRARY_PATH=B.FAKE_NVML_DIR + ":" + os.environ.get("LD_LIBRARY_PATH", ""), WORLD_SIZE="2")
+    env = dict(os.environ, GFD_FAKE_NVML=fix, LD_LIBRARY_PATH=B.FAKE_NVML_DIR + ":" + os.environ.get("LD_LIBRARY_PATH", ""), WORLD_SIZE="2",
+               GFD_BENCH_SETTLE_S="0")  # no GPU here whose power state could settle
     r1 = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference", "--gpus", "2", "--steps", "3", "--warmup", "3"],
                         env=dict(env, RANK="1"), capture_output=True, text=True, timeout=120)
     assert r1.returncode == 0 and r1.stdout.strip() == ""
