@@ -31,14 +31,62 @@ namespace {
 
 [[noreturn]] void fail(const std::string &m) { throw ParseError("yaml: " + m); }
 
-bool all_digits(const std::string &s, size_t from) {
-    if (from >= s.size()) return false;
-    for (size_t i = from; i < s.size(); i++)
-        if (!(std::isdigit((unsigned char)s[i]) || s[i] == '_')) return false;
+// strconv.ParseInt(s, 0, 64) / ParseUint: optional sign (ParseInt only), then 0x / 0b / 0o prefixes, a leading 0 = octal,
+// else decimal; at least one digit; every digit valid for the base; no overflow.  (Underscores are gone by now: yaml.v2
+// strips them before it calls ParseInt, resolve.go:147.)
+bool go_parse_int(const std::string &s, bool allow_sign, bool *negative, unsigned long long *magnitude) {
+    size_t i = 0;
+    *negative = false;
+    if (allow_sign && i < s.size() && (s[i] == '+' || s[i] == '-')) { *negative = s[i] == '-'; i++; }
+    int base = 10;
+    if (i + 1 < s.size() && s[i] == '0') {
+        char p = s[i + 1];
+        if (p == 'x' || p == 'X') { base = 16; i += 2; }
+        else if (p == 'b' || p == 'B') { base = 2; i += 2; }
+        else if (p == 'o' || p == 'O') { base = 8; i += 2; }
+        else { base = 8; i += 1; }
+    }
+    if (i >= s.size()) return false;
+    unsigned long long acc = 0;
+    for (; i < s.size(); i++) {
+        char c = s[i];
+        int d = (c >= '0' && c <= '9') ? c - '0' : (c >= 'a' && c <= 'f') ? c - 'a' + 10 : (c >= 'A' && c <= 'F') ? c - 'A' + 10 : 99;
+        if (d >= base) return false;
+        if (acc > (~0ull - (unsigned)d) / (unsigned)base) return false;  // overflow of uint64
+        acc = acc * (unsigned)base + (unsigned)d;
+    }
+    *magnitude = acc;
     return true;
 }
 
-// yaml.v2 resolve(): plain scalar -> typed value
+// yamlStyleFloat (resolve.go:84): ^[-+]?(\.[0-9]+|[0-9]+(\.[0-9]*)?)([eE][-+]?[0-9]+)?$
+bool yaml_style_float(const std::string &s) {
+    size_t i = 0, n = s.size();
+    if (i < n && (s[i] == '+' || s[i] == '-')) i++;
+    size_t d0 = i;
+    while (i < n && std::isdigit((unsigned char)s[i])) i++;
+    if (i > d0) {
+        if (i < n && s[i] == '.') { i++; while (i < n && std::isdigit((unsigned char)s[i])) i++; }
+    } else {
+        if (i >= n || s[i] != '.') return false;
+        i++;
+        size_t f0 = i;
+        while (i < n && std::isdigit((unsigned char)s[i])) i++;
+        if (i == f0) return false;
+    }
+    if (i < n && (s[i] == 'e' || s[i] == 'E')) {
+        i++;
+        if (i < n && (s[i] == '+' || s[i] == '-')) i++;
+        size_t e0 = i;
+        while (i < n && std::isdigit((unsigned char)s[i])) i++;
+        if (i == e0) return false;
+    }
+    return i == n;
+}
+
+// yaml.v2 resolve() (resolve.go:86-207) for a plain scalar with no tag: the fixed map of null / bool / inf / nan words, then by
+// first character: a digit or a sign -> int (Go base-0 syntax, so 017 is 15 and 0b11 is 3), unsigned, float by yamlStyleFloat;
+// a dot -> float; anything else a string.  Not done: the timestamp forms (2001-12-14 ...), which stay strings here.
 Value resolve_plain(const std::string &s) {
     Value v;
     if (s.empty() || s == "~" || s == "null" || s == "Null" || s == "NULL") return v;
@@ -46,39 +94,44 @@ Value resolve_plain(const std::string &s) {
     static const char *F[] = {"n", "N", "no", "No", "NO", "false", "False", "FALSE", "off", "Off", "OFF"};
     for (const char *t : T) if (s == t) { v.kind = Value::Bool; v.b = true; return v; }
     for (const char *f : F) if (s == f) { v.kind = Value::Bool; v.b = false; return v; }
-    size_t st = (s[0] == '-' || s[0] == '+') ? 1 : 0;
-    std::string plain;
-    for (char c : s) if (c != '_') plain += c;
-    if (all_digits(s, st)) {
-        errno = 0;
-        char *end = nullptr;
-        long long x = strtoll(plain.c_str(), &end, 10);
-        if (errno == 0 && end && *end == 0) { v.kind = Value::Int; v.i = x; v.s = s; return v; }
-    }
-    if (s.size() > st + 2 && s[st] == '0' && (s[st + 1] == 'x' || s[st + 1] == 'X')) {
-        errno = 0;
-        char *end = nullptr;
-        long long x = strtoll(plain.c_str(), &end, 16);
-        if (errno == 0 && end && *end == 0) { v.kind = Value::Int; v.i = x; v.s = s; return v; }
-    }
-    // float: needs a digit and only float characters
-    bool digit = false, ok = true;
-    for (size_t i = st; i < s.size() && ok; i++) {
-        char c = s[i];
-        if (std::isdigit((unsigned char)c)) digit = true;
-        else if (!(c == '.' || c == 'e' || c == 'E' || c == '-' || c == '+' || c == '_')) ok = false;
-    }
-    if (ok && digit) {
-        char *end = nullptr;
-        double d = strtod(plain.c_str(), &end);
-        if (end && *end == 0) { v.kind = Value::Float; v.f = d; v.s = s; return v; }
-    }
-    if (s == ".inf" || s == ".Inf" || s == ".INF" || s == "+.inf") { v.kind = Value::Float; v.f = INFINITY; v.s = s; return v; }
+    if (s == ".inf" || s == ".Inf" || s == ".INF" || s == "+.inf" || s == "+.Inf" || s == "+.INF") { v.kind = Value::Float; v.f = INFINITY; v.s = s; return v; }
     if (s == "-.inf" || s == "-.Inf" || s == "-.INF") { v.kind = Value::Float; v.f = -INFINITY; v.s = s; return v; }
     if (s == ".nan" || s == ".NaN" || s == ".NAN") { v.kind = Value::Float; v.f = NAN; v.s = s; return v; }
-    v.kind = Value::String;
-    v.s = s;
-    return v;
+    auto as_string = [&] { v.kind = Value::String; v.s = s; return v; };
+    auto as_float = [&](const std::string &text) {
+        char *end = nullptr;
+        errno = 0;
+        double d = strtod(text.c_str(), &end);
+        if (!end || *end != 0) return false;
+        v.kind = Value::Float;
+        v.f = d;
+        v.s = s;
+        return true;
+    };
+    const char c0 = s[0];
+    if (c0 == '.') {  // hint '.': strconv.ParseFloat(in) on the text as it stands
+        if (yaml_style_float(s) && as_float(s)) return v;
+        return as_string();
+    }
+    if (!(std::isdigit((unsigned char)c0) || c0 == '+' || c0 == '-')) return as_string();
+    std::string plain;
+    for (char c : s) if (c != '_') plain += c;
+    bool neg = false;
+    unsigned long long mag = 0;
+    if (go_parse_int(plain, true, &neg, &mag) && (neg ? mag <= 9223372036854775808ull : mag <= 9223372036854775807ull)) {
+        v.kind = Value::Int;
+        v.i = neg ? (int64_t)(0ull - mag) : (int64_t)mag;
+        v.s = s;
+        return v;
+    }
+    if (go_parse_int(plain, false, &neg, &mag)) {  // ParseUint: above int64 -- kept as a float here (no field of the config takes one)
+        v.kind = Value::Float;
+        v.f = (double)mag;
+        v.s = s;
+        return v;
+    }
+    if (yaml_style_float(plain) && as_float(plain)) return v;
+    return as_string();
 }
 
 void append_utf8(std::string &o, uint32_t cp) {
