@@ -493,25 +493,6 @@ def main():
     kernel_ms = e0.elapsed_time(e1) / args.steps
     probe_gbps = PROBE_BYTES / (kernel_ms * 1e-3) / 1e9
     checksum = tuple(int(v) for v in d_out.cpu().numpy().view(np.uint64))
-    # the other two HBM kernels of the library, timed the same way (reported beside the dominant one, not instead of it)
-    other_kernels = []
-    dst = torch.empty(PROBE_BYTES, dtype=torch.uint8, device=dev)
-    for kname, algorithmic, call in (
-            ("hbm_copy_kernel", 2 * PROBE_BYTES, lambda: B.hbm_copy(dst.data_ptr(), buf.data_ptr(), PROBE_BYTES, stream.cuda_stream)),
-            ("fill_pattern_kernel", PROBE_BYTES, lambda: B.hbm_fill_pattern(dst.data_ptr(), PROBE_BYTES, 1, stream.cuda_stream))):
-        for _ in range(args.warmup):
-            call()
-        k0, k1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        k0.record(stream)
-        for _ in range(args.steps):
-            call()
-        k1.record(stream)
-        torch.cuda.synchronize()
-        launches += args.warmup + args.steps
-        ms = k0.elapsed_time(k1) / args.steps
-        other_kernels.append({"kernel": kname, "bound": "hbm", "algorithmic_bytes_per_launch": algorithmic, "ms_per_launch": round(ms, 5),
-                              "achieved": round(algorithmic / (ms * 1e-3) / 1e9, 1), "unit": "GB/s"})
-    del dst
     sampler.stop()
     clocks = sampler.summary()
 
@@ -605,7 +586,6 @@ def main():
                      "kernel": "hbm_read_fold_kernel (one launch per checksum; the last CTA folds the partials)",
                      "algorithmic_bytes_per_launch": PROBE_BYTES, "ms_per_launch": round(kernel_ms, 5),
                      "frac_of_nominal_7700": round(probe_gbps / 7700.0, 4)},
-        "roofline_other_kernels": [dict(k, peak=peak, frac=round(k["achieved"] / peak, 4)) for k in other_kernels],
         "cpu_baseline": {"value": rep_st["median"], "unit": "ms", "cores": 1, "kind": "port",
                          "sample": "%d passes of oracle/ref_replay (C replay of the reference's NVML call sequence: %d NVML calls + %d dlopen "
                                    "cycles per pass) INTERLEAVED with the product's passes, chunks of %d, same device cap"
