@@ -318,3 +318,20 @@ def test_random_sizes_and_offsets(env):
         torch.cuda.synchronize()
         got = dst.cpu().numpy()
         assert np.array_equal(got[:n], host[off:off + n]) and (got[n:n + 64] == 0x5A).all(), (off, n)
+
+
+def test_copy_and_checksum_take_peer_pointers_without_prior_setup(env):
+    """gfd_hbm_copy / gfd_hbm_read_checksum with the source on another GPU: the library enables the peer mapping itself (the kernel
+    runs on the destination's GPU and pulls over NVLink); bytes arrive intact.  Needs >= 2 GPUs."""
+    torch, B = env.torch, env.B
+    if torch.cuda.device_count() < 2 or not torch.cuda.can_device_access_peer(0, 1):
+        pytest.skip("needs 2 peer-capable GPUs")
+    n = (6 << 20) + 40
+    host = np.random.default_rng(77).integers(0, 256, size=n, dtype=np.uint8)
+    far = torch.from_numpy(host).to("cuda:1")
+    near = torch.zeros(n, dtype=torch.uint8, device=env.dev)
+    torch.cuda.synchronize()
+    B.hbm_copy(near.data_ptr(), far.data_ptr(), n, torch.cuda.current_stream().cuda_stream)
+    torch.cuda.synchronize()
+    assert bool((near.cpu() == torch.from_numpy(host)).all())
+    assert gpu_checksum(env, far, nbytes=n) == oracle_checksum(env, host) == gpu_checksum(env, near, nbytes=n)
