@@ -182,6 +182,19 @@ struct Flow {
         }
     }
 
+    // A line break inside a quoted scalar (YAML line folding): white space around it goes, one break reads as a space,
+    // k + 1 breaks in a row (k empty lines) read as k newlines.  p stands just after the first '\n'.
+    void fold_break(std::string &o) {
+        while (!o.empty() && (o.back() == ' ' || o.back() == '\t')) o.pop_back();
+        size_t breaks = 1;
+        while (p < t.size() && (t[p] == ' ' || t[p] == '\t' || t[p] == '\n' || t[p] == '\r')) {
+            if (t[p] == '\n') breaks++;
+            p++;
+        }
+        if (breaks == 1) o += ' ';
+        else o.append(breaks - 1, '\n');
+    }
+
     std::string dquoted() {
         std::string o;
         p++;  // opening quote
@@ -189,10 +202,16 @@ struct Flow {
             if (p >= t.size()) fail("unterminated double-quoted scalar");
             char c = t[p++];
             if (c == '"') break;
-            if (c == '\n') fail("unterminated quoted scalar on this line (scalars continued on a following line are not supported)");
+            if (c == '\r' && p < t.size() && t[p] == '\n') continue;
+            if (c == '\n') { fold_break(o); continue; }
             if (c != '\\') { o += c; continue; }
             if (p >= t.size()) fail("bad escape");
             char e = t[p++];
+            if (e == '\r' && p < t.size() && t[p] == '\n') e = t[p++];
+            if (e == '\n') {  // escaped line break: the lines join with nothing in between, leading blanks of the next line go
+                while (p < t.size() && (t[p] == ' ' || t[p] == '\t')) p++;
+                continue;
+            }
             switch (e) {
             case 'n': o += '\n'; break;
             case 't': o += '\t'; break;
@@ -232,7 +251,8 @@ struct Flow {
                 if (p < t.size() && t[p] == '\'') { o += '\''; p++; continue; }
                 break;
             }
-            if (c == '\n') fail("unterminated quoted scalar on this line (scalars continued on a following line are not supported)");
+            if (c == '\r' && p < t.size() && t[p] == '\n') continue;
+            if (c == '\n') { fold_break(o); continue; }
             o += c;
         }
         return o;
@@ -401,6 +421,38 @@ struct Block {
 
     bool is_dash(const std::string &t) const { return t == "-" || t.compare(0, 2, "- ") == 0; }
 
+    // Is `text` (a value that starts with a quote or a flow bracket) still open at its end -- inside quotes, or with brackets unbalanced?
+    static bool still_open(const std::string &text) {
+        int depth = 0;
+        char quote = 0;
+        for (size_t i = 0; i < text.size(); i++) {
+            char c = text[i];
+            if (quote == '"') { if (c == '\\') i++; else if (c == '"') quote = 0; continue; }
+            if (quote == '\'') { if (c == '\'') { if (i + 1 < text.size() && text[i + 1] == '\'') i++; else quote = 0; } continue; }
+            if (c == '"' || c == '\'') quote = c;
+            else if (c == '[' || c == '{') depth++;
+            else if (c == ']' || c == '}') depth--;
+            else if (c == '#' && (i == 0 || text[i - 1] == ' ' || text[i - 1] == '\t' || text[i - 1] == '\n')) {
+                while (i < text.size() && text[i] != '\n') i++;  // a comment inside a flow collection
+            }
+        }
+        return quote != 0 || depth > 0;
+    }
+
+    // A quoted scalar or a flow collection may run over several physical lines: append the following RAW lines (comment
+    // stripping is not safe inside quotes) until it closes, and step pos past them.  `head` = index of the line it started on.
+    std::string gather(std::string text, size_t head) {
+        if (text.empty() || !(text[0] == '"' || text[0] == '\'' || text[0] == '[' || text[0] == '{') || !still_open(text)) return text;
+        // restart from the raw line: the stripped text may have lost a '#...' that was inside quotes further on
+        size_t r = lines[head].raw + 1;
+        while (r < raw.size() && still_open(text)) {
+            text += "\n" + raw[r];
+            r++;
+        }
+        while (pos < lines.size() && lines[pos].raw < r) pos++;
+        return text;
+    }
+
     Value scalar_or_flow(const std::string &text, const std::string &tag) {
         if (text.empty()) return apply_scalar_tag(tag, "", Value());
         char c = text[0];
@@ -426,7 +478,11 @@ struct Block {
         if (quoted) *quoted = false;
         if (!t.empty() && (t[0] == '"' || t[0] == '\'')) {
             Flow f(t);
-            *key = t[0] == '"' ? f.dquoted() : f.squoted();
+            try {
+                *key = t[0] == '"' ? f.dquoted() : f.squoted();
+            } catch (const ParseError &) {
+                return false;  // a quoted SCALAR that continues on the next line, not a key
+            }
             if (quoted) *quoted = true;
             i = f.p;
             while (i < t.size() && t[i] == ' ') i++;
@@ -520,7 +576,7 @@ struct Block {
             Value bs = block_scalar(rest, head, indent);
             v = props.tag.empty() ? bs : apply_scalar_tag(props.tag, bs.s, bs);
         } else if (!rest.empty()) {
-            v = scalar_or_flow(rest, props.tag);
+            v = scalar_or_flow(gather(rest, head), props.tag);
         } else if (pos < lines.size() &&
                    (lines[pos].indent > indent || (allow_same_indent_seq && lines[pos].indent == indent && is_dash(lines[pos].text)))) {
             v = parse_node(lines[pos].indent);

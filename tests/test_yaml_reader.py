@@ -95,7 +95,7 @@ def shared_doc(draw):
 
 
 @settings(max_examples=400, deadline=None, suppress_health_check=[HealthCheck.too_slow, HealthCheck.filter_too_much])
-@given(doc=st.one_of(TREE, shared_doc()), style=st.sampled_from(["block", "block4", "literal", "folded", "flow_leaves", "explicit_start"]))
+@given(doc=st.one_of(TREE, shared_doc()), style=st.sampled_from(["block", "block4", "literal", "folded", "flow_leaves", "explicit_start", "wrapped", "flow_wrapped"]))
 def test_reader_agrees_with_pyyaml(doc, style):
     def has_yn(x):
         # Known differences between the two real implementations, not tested here (the hand-written cases below pin what yaml.v2
@@ -123,6 +123,11 @@ def test_reader_agrees_with_pyyaml(doc, style):
     elif style == "explicit_start":
         kw["explicit_start"] = True
         kw["version"] = (1, 1)
+    elif style == "wrapped":          # narrow page: PyYAML continues quoted (and plain) scalars on following lines
+        kw["width"] = 24
+    elif style == "flow_wrapped":     # flow collections broken over several lines
+        kw["width"] = 24
+        kw["default_flow_style"] = True
     text = yaml.dump(doc, Dumper=dumper, **kw)
     try:
         want = yaml.safe_load(text)
@@ -130,8 +135,8 @@ def test_reader_agrees_with_pyyaml(doc, style):
         return
     status, got = product_parse(text)
     if status == "error":
-        # the documented refusals: a scalar or flow collection continued on a following line (PyYAML breaks long or
-        # multi-line quoted scalars that way)
+        # the documented refusal: a PLAIN scalar continued on a following line (PyYAML breaks long plain scalars that way on a
+        # narrow page); quoted scalars and flow collections over several lines are read
         assert any(m in got for m in ("unterminated", "could not parse line", "expected 'key: value'", "bad indentation", "trailing characters",
                                        "expected ',' or")), (text, got)
         return
@@ -159,6 +164,12 @@ HAND = [
     ("s: >-\n  one\n  two\n", {"s": "one two"}),
     ("- |\n  item\n- >-\n  folded\n  item\n", ["item\n", "folded item"]),
     ("s: |\n\nt: 1\n", {"s": "", "t": 1}),
+    # quoted scalars and flow collections over several lines (line folding inside quotes; an escaped break joins)
+    ("a: [1,\n  2, # c\n  {k: \"x\n     y\"}\n  ]\nb: \"one\n  two\n\n  three\\\n  four\"\nc: 's1\n  s2'\nd: ok\n",
+     {"a": [1, 2, {"k": "x y"}], "b": "one two\nthreefour", "c": "s1 s2", "d": "ok"}),
+    ("sharing:\n  timeSlicing:\n    resources: [\n      {name: nvidia.com/gpu,\n       replicas: 2}\n    ]\n",
+     {"sharing": {"timeSlicing": {"resources": [{"name": "nvidia.com/gpu", "replicas": 2}]}}}),
+    ("- \"a # not a comment\n  b\"\n- x\n", ["a # not a comment b", "x"]),
     # tags
     ("a: !!str 123\nb: !!int \"7\"\nc: !!float 1\nd: !custom x\ne: !!str true\nf: !!null ''\n", {"a": "123", "b": 7, "c": 1.0, "d": "x", "e": "true", "f": None}),
     ("a: !!map {k: v}\nb: !!seq [1]\n", {"a": {"k": "v"}, "b": [1]}),
@@ -185,7 +196,8 @@ def test_hand_written_documents(text, want):
     ("a: &x 1\nb:\n  <<: *x\n", "map merge requires"),
     ("a: !!binary aGk=\n", "unsupported YAML feature"),
     ("a: |x\n  t\n", "bad block scalar header"),
-    ("a: \"two\n  lines\"\n", "unterminated"),
+    ("a: \"never closed\n  at all\n", "unterminated"),
+    ("a: plain scalar\n  continued here\n", "bad indentation"),
     ("\tkey: v\n", "tabs"),
 ])
 def test_refusals_are_loud(text, needle):
