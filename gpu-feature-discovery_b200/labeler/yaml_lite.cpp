@@ -353,14 +353,28 @@ struct Flow {
         }
         if (c == '"') { v.kind = Value::String; v.s = dquoted(); v.quoted = true; return v; }
         if (c == '\'') { v.kind = Value::String; v.s = squoted(); v.quoted = true; return v; }
-        size_t s = p;
-        while (p < t.size() && t[p] != ',' && t[p] != '}' && t[p] != ']' && t[p] != '\n') {
-            if (t[p] == ':' && (p + 1 >= t.size() || t[p + 1] == ' ')) break;
-            if (t[p] == '#' && p > s && std::isspace((unsigned char)t[p - 1])) break;
-            p++;
+        // plain scalar in flow context; it may continue over line breaks (folded: one break = a space, k empty lines = k newlines)
+        std::string plain;
+        bool multi = false;
+        while (true) {
+            size_t s = p;
+            while (p < t.size() && t[p] != ',' && t[p] != '}' && t[p] != ']' && t[p] != '\n') {
+                if (t[p] == ':' && (p + 1 >= t.size() || t[p + 1] == ' ' || t[p + 1] == '\n')) break;
+                if (t[p] == '#' && p > s && std::isspace((unsigned char)t[p - 1])) break;
+                p++;
+            }
+            std::string seg = t.substr(s, p - s);
+            while (!seg.empty() && std::isspace((unsigned char)seg.back())) seg.pop_back();
+            plain += seg;
+            if (p >= t.size() || t[p] != '\n') break;
+            size_t q = p, breaks = 0;
+            while (q < t.size() && (t[q] == ' ' || t[q] == '\t' || t[q] == '\n' || t[q] == '\r')) { if (t[q] == '\n') breaks++; q++; }
+            if (q >= t.size() || t[q] == ',' || t[q] == ']' || t[q] == '}' || t[q] == '#' || plain.empty()) break;
+            if (breaks == 1) plain += ' '; else plain.append(breaks - 1, '\n');
+            p = q;
+            multi = true;
         }
-        std::string plain = t.substr(s, p - s);
-        while (!plain.empty() && std::isspace((unsigned char)plain.back())) plain.pop_back();
+        if (multi) { Value sv; sv.kind = Value::String; sv.s = plain; return sv; }
         return resolve_plain(plain);
     }
 };
@@ -576,7 +590,34 @@ struct Block {
             Value bs = block_scalar(rest, head, indent);
             v = props.tag.empty() ? bs : apply_scalar_tag(props.tag, bs.s, bs);
         } else if (!rest.empty()) {
-            v = scalar_or_flow(gather(rest, head), props.tag);
+            const char c = rest[0];
+            if (c == '"' || c == '\'' || c == '[' || c == '{' || c == '*') {
+                v = scalar_or_flow(gather(rest, head), props.tag);
+            } else {
+                // a plain scalar may continue on following, deeper-indented lines: one break folds to a space, k empty lines
+                // in between to k newlines; a multi-line plain scalar is always a string
+                std::string text = rest;
+                bool multi = false;
+                size_t last_raw = lines[head].raw;
+                while (pos < lines.size() && lines[pos].indent > indent) {
+                    const std::string &t = lines[pos].text;
+                    std::string k, r;
+                    if (is_dash(t) ? false : split_key(t, &k, &r)) fail("mapping values are not allowed in this context: " + t);
+                    size_t blanks = lines[pos].raw - last_raw - 1;
+                    if (blanks) text.append(blanks, '\n'); else text += ' ';
+                    text += t;
+                    last_raw = lines[pos].raw;
+                    multi = true;
+                    pos++;
+                }
+                if (multi) {
+                    v.kind = Value::String;
+                    v.s = text;
+                    v = props.tag.empty() ? v : apply_scalar_tag(props.tag, text, v);
+                } else {
+                    v = scalar_or_flow(text, props.tag);
+                }
+            }
         } else if (pos < lines.size() &&
                    (lines[pos].indent > indent || (allow_same_indent_seq && lines[pos].indent == indent && is_dash(lines[pos].text)))) {
             v = parse_node(lines[pos].indent);

@@ -6,9 +6,9 @@
 // YAML 1.1 scalar resolution as yaml.v2 does it (null/bool/int/float/string), anchors / aliases / merge keys ("<<", applied
 // where they stand, as yaml.v2 does), core and local tags on scalars, literal and folded block scalars with chomping and
 // indentation indicators, directives, and "first document only" for multi-document files (yaml.v2's Unmarshal).
-// Quoted scalars and flow collections may continue on following lines (quoted scalars with YAML's line folding).
-// Still refused with a parse error: PLAIN scalars that continue on a following line, complex keys ("? "), properties in
-// front of an implicit key ("&a key: v"), !!binary, tab indentation.
+// Plain and quoted scalars and flow collections may continue on following lines (scalars with YAML's line folding).
+// Still refused with a parse error: complex keys ("? "), properties in front of an implicit key ("&a key: v"), !!binary,
+// tab indentation.
 #pragma once
 #include <cstdint>
 #include <stdexcept>
