@@ -16,6 +16,8 @@
 
 #include <cstdio>
 #include <cstring>
+#include <functional>
+#include <system_error>
 #include <thread>
 
 #include "gfd_internal.h"
@@ -538,9 +540,29 @@ GFD_API int gfd_prefetch(gfd_mgr *m, int threads) {
     // dlopen libcuda (~0.4 ms) and nothing it needs waits for a GPU attach.  Joined on every path out of this function.
     struct SystemQueries {
         std::thread t;
-        explicit SystemQueries(gfd_mgr *m) : t([m] { q_driver_version(m); q_cuda_version(m); }) {}
+        explicit SystemQueries(gfd_mgr *m) {
+            try {
+                t = std::thread([m] { q_driver_version(m); q_cuda_version(m); });
+            } catch (const std::system_error &) {
+                // no thread to be had (a pids limit on the pod): the getters ask on demand, as they do without gfd_prefetch
+            }
+        }
         ~SystemQueries() { if (t.joinable()) t.join(); }
     } system_queries(m);
+    // nt workers = up to nt-1 helper threads + the calling thread, which always takes part: a helper that cannot be created is
+    // simply not there and the work still gets done.
+    auto run_workers = [&pool](size_t nt, const std::function<void()> &fn) {
+        for (size_t t = 1; t < nt; t++) {
+            try {
+                pool.emplace_back(fn);
+            } catch (const std::system_error &) {
+                break;
+            }
+        }
+        fn();
+        for (auto &t : pool) t.join();
+        pool.clear();
+    };
     if (!m->devices.done) {
         // Threaded walk.  nvmlDeviceGetHandleByIndex is where the driver attaches a GPU (~8 ms each on B200, measured
         // in profiles/r1_nvml_phase_timing.txt), so on a multi-GPU node the attach itself is what gets spread over
@@ -560,19 +582,17 @@ GFD_API int gfd_prefetch(gfd_mgr *m, int threads) {
         std::vector<std::unique_ptr<gfd_dev>> slots(count);
         std::vector<int> handle_rc(count, 0);
         size_t nt = std::min((size_t)count, (size_t)threads);
-        for (size_t t = 0; t < nt; t++)
-            pool.emplace_back([&] {
-                for (size_t i = next.fetch_add(1); i < count; i = next.fetch_add(1)) {
-                    nvmlDevice_t h = nullptr;
-                    handle_rc[i] = NVCALL(m, DeviceGetHandleByIndex, (unsigned)i, &h);
-                    if (handle_rc[i]) continue;
-                    slots[i].reset(new gfd_dev());
-                    slots[i]->mgr = m;
-                    slots[i]->h = h;
-                    if (q_name_raw(slots[i].get()) == 0 && slots[i]->name.v != "NVIDIA DGX Display") prefetch_one(slots[i].get());
-                }
-            });
-        for (auto &t : pool) t.join();
+        run_workers(nt, [&] {
+            for (size_t i = next.fetch_add(1); i < count; i = next.fetch_add(1)) {
+                nvmlDevice_t h = nullptr;
+                handle_rc[i] = NVCALL(m, DeviceGetHandleByIndex, (unsigned)i, &h);
+                if (handle_rc[i]) continue;
+                slots[i].reset(new gfd_dev());
+                slots[i]->mgr = m;
+                slots[i]->h = h;
+                if (q_name_raw(slots[i].get()) == 0 && slots[i]->name.v != "NVIDIA DGX Display") prefetch_one(slots[i].get());
+            }
+        });
         for (unsigned i = 0; i < count; i++) {
             int e = handle_rc[i] ? handle_rc[i] : slots[i]->name.rc;
             if (e) { m->devices.v.clear(); m->devices.rc = e; return 0; }
@@ -586,11 +606,9 @@ GFD_API int gfd_prefetch(gfd_mgr *m, int threads) {
     size_t n = m->devices.v.size();
     if (n < 2) return 0;
     size_t nt = std::min(n, (size_t)threads);
-    for (size_t t = 0; t < nt; t++)
-        pool.emplace_back([&] {
-            for (size_t i = next.fetch_add(1); i < n; i = next.fetch_add(1)) prefetch_one(m->devices.v[i].get());
-        });
-    for (auto &t : pool) t.join();
+    run_workers(nt, [&] {
+        for (size_t i = next.fetch_add(1); i < n; i = next.fetch_add(1)) prefetch_one(m->devices.v[i].get());
+    });
     return 0;
 }
 

@@ -9,6 +9,7 @@
 #include <cstring>
 #include <ctime>
 #include <string>
+#include <system_error>
 #include <thread>
 #include <exception>
 
@@ -68,13 +69,20 @@ bool run(gfdlm::Manager &mgr, const gfdcfg::Config &config, const sigset_t &sigs
         // labelers.Labels(), after the NVML labeler has been built: main.go:160-172), so an NVML failure still wins.
         gfdlm::Labels vgpu;
         std::exception_ptr vgpu_error;
-        std::thread vgpu_thread([&] {
+        auto scan = [&] {
             try {
                 vgpu = gfdlm::vgpu_labels(config);
             } catch (...) {
                 vgpu_error = std::current_exception();
             }
-        });
+        };
+        std::thread vgpu_thread;
+        try {
+            vgpu_thread = std::thread(scan);
+        } catch (const std::system_error &) {
+            // no thread to be had (a pids limit on the pod): the scan runs after the NVML bracket, where the reference has it
+        }
+        const bool scan_in_thread = vgpu_thread.joinable();
         struct Join {
             std::thread &t;
             ~Join() { if (t.joinable()) t.join(); }
@@ -83,7 +91,8 @@ bool run(gfdlm::Manager &mgr, const gfdcfg::Config &config, const sigset_t &sigs
         double t1 = now_ms();
         gfdlm::Labels labels = timestamp;                      // lm.Merge(timestampLabeler, loopLabelers): later wins
         for (auto &kv : nvml) labels[kv.first] = kv.second;
-        vgpu_thread.join();
+        if (scan_in_thread) vgpu_thread.join();
+        else scan();
         try {
             if (vgpu_error) std::rethrow_exception(vgpu_error);
         } catch (const gfdlm::PassError &e) {

@@ -45,3 +45,21 @@ def test_single_gpu_node_takes_the_serial_path(tmp_path):
     auto, text0 = timed_passes(tmp_path, "c2_1xB200", 0, latency_us=1000)
     assert text1 == text0
     assert abs(auto - serial) < max(3.0, 0.5 * serial), (serial, auto)  # nothing to spread: same cost, no thread overhead to speak of
+
+
+def test_pass_survives_a_host_that_refuses_new_threads(tmp_path):
+    """A pod with a pids limit can refuse pthread_create (EAGAIN).  The per-GPU helpers, the node-level query thread and the vGPU
+    scan thread are all optional: with every thread creation failing the pass must still produce the same file, serially."""
+    import subprocess
+    from test_cli_parity import NODES, cli_pass, oracle_pass
+    shim_c = os.path.join(str(tmp_path), "nothreads.c")
+    shim_so = os.path.join(str(tmp_path), "nothreads.so")
+    open(shim_c, "w").write("#include <errno.h>\n#include <pthread.h>\n"
+                            "int pthread_create(pthread_t *t, const pthread_attr_t *a, void *(*f)(void *), void *arg) {\n"
+                            "    (void)t; (void)a; (void)f; (void)arg; return EAGAIN;\n}\n")
+    subprocess.run(["gcc", "-shared", "-fPIC", "-o", shim_so, shim_c], check=True)
+    for name, strategy in (("c3_8xB200", "none"), ("c4_single_8x7x1g23", "single"), ("c5_mixed_hetero", "mixed")):
+        want, _ = oracle_pass(NODES[name], strategy)
+        rc, got, stderr, _ = cli_pass(tmp_path, NODES[name], strategy, extra_env={"LD_PRELOAD": shim_so})
+        assert rc == 0, stderr
+        assert got == want
