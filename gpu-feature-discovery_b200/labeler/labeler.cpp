@@ -13,6 +13,7 @@
 #include <cstring>
 #include <fstream>
 #include <sstream>
+#include <system_error>
 #include <thread>
 
 #include "go_compat.hpp"
@@ -552,8 +553,7 @@ Labels probe_labels(const gfdcfg::Config &config) {
         struct PerGpu { int rc = 0; const char *what = ""; double read = 0, copy = 0, write = 0; size_t used = 0; };
         std::vector<PerGpu> res((size_t)n);
         std::vector<std::thread> pool;
-        for (int d = 0; d < n; d++)
-            pool.emplace_back([&, d] {
+        auto probe_gpu = [&](int d) {
                 PerGpu &g = res[(size_t)d];
                 gfd_probe_result r;
                 size_t used = 0;
@@ -563,7 +563,14 @@ Labels probe_labels(const gfdcfg::Config &config) {
                 g.copy = r.gbps;
                 if ((g.rc = run(d, (size_t)config.probe_bytes, GFD_PROBE_WRITE, &r, &used))) { g.what = "HBM write probe failed on GPU "; return; }
                 g.write = r.gbps;
-            });
+            };
+        for (int d = 0; d < n; d++) {
+            try {
+                pool.emplace_back(probe_gpu, d);
+            } catch (const std::system_error &) {
+                probe_gpu(d);  // no thread to be had: this GPU is probed here, after the others were started
+            }
+        }
         for (auto &t : pool) t.join();
         double rmin = 1e30, cmin = 1e30, wmin = 1e30;
         size_t size_min = (size_t)config.probe_bytes;
