@@ -134,6 +134,20 @@ Value resolve_plain(const std::string &s) {
     return as_string();
 }
 
+// A mapping key ends up as a JSON object key: yaml.v2 resolves an unquoted key like any plain scalar and sigs.k8s.io/yaml turns
+// the typed key back into a string (yaml.go:176-206): 010 becomes "8", yes becomes "true"; a null key is refused there.
+// (Float keys keep their spelling here; the reference would print them with strconv 'g'.)
+std::string key_string(const std::string &raw, bool quoted) {
+    if (quoted) return raw;
+    Value v = resolve_plain(raw);
+    switch (v.kind) {
+    case Value::Int: return std::to_string(v.i);
+    case Value::Bool: return v.b ? "true" : "false";
+    case Value::Null: fail("unsupported map key of type null: " + raw);
+    default: return raw;
+    }
+}
+
 void append_utf8(std::string &o, uint32_t cp) {
     if (cp < 0x80) o += (char)cp;
     else if (cp < 0x800) { o += (char)(0xC0 | (cp >> 6)); o += (char)(0x80 | (cp & 0x3F)); }
@@ -326,9 +340,10 @@ struct Flow {
                         }
                     }
                 } else {
+                    const std::string ks = key_string(key, key_quoted);
                     bool dup = false;
-                    for (auto &kv : v.obj) if (kv.first == key) { kv.second = val; dup = true; }
-                    if (!dup) v.obj.emplace_back(key, val);
+                    for (auto &kv : v.obj) if (kv.first == ks) { kv.second = val; dup = true; }
+                    if (!dup) v.obj.emplace_back(ks, val);
                 }
                 ws();
                 if (p < t.size() && t[p] == ',') { p++; ws(); if (p < t.size() && t[p] == '}') { p++; break; } continue; }
@@ -696,7 +711,7 @@ struct Block {
             pos++;
             Value val = value_after(rest, indent, head, true);
             if (key == "<<" && !quoted) map_merge(v, val);
-            else map_put(v, key, val);
+            else map_put(v, key_string(key, quoted), val);
         }
         if (pos < lines.size() && lines[pos].indent > indent) fail("bad indentation at: " + lines[pos].text);
         return v;

@@ -140,13 +140,13 @@ def test_reader_agrees_with_pyyaml(doc, style):
 
 HAND = [
     # merge keys: the usual form, a list of maps (earlier wins), and yaml.v2's "where it stands" rule
-    ("a: &a {x: 1, y: 2}\nb:\n  <<: *a\n  y: 3\n", {"a": {"x": 1, "y": 2}, "b": {"x": 1, "y": 3}}),
+    ("a: &a {x: 1, w: 2}\nb:\n  <<: *a\n  w: 3\n", {"a": {"x": 1, "w": 2}, "b": {"x": 1, "w": 3}}),
     ("a: &a {x: 1}\nb: &b {x: 2, z: 9}\nc:\n  <<: [*a, *b]\n", {"a": {"x": 1}, "b": {"x": 2, "z": 9}, "c": {"x": 1, "z": 9}}),
-    ("a: &a {y: 2}\nb:\n  y: 3\n  <<: *a\n", {"a": {"y": 2}, "b": {"y": 2}}),          # decode.go:660-664: the merge overwrites the earlier key
-    ("a: &a {y: 2}\nb: {y: 3, <<: *a, z: 1}\n", {"a": {"y": 2}, "b": {"y": 2, "z": 1}}),
-    ("a: &a {y: 2}\nb:\n  \"<<\": *a\n", {"a": {"y": 2}, "b": {"<<": {"y": 2}}}),      # a quoted "<<" is an ordinary key
+    ("a: &a {w: 2}\nb:\n  w: 3\n  <<: *a\n", {"a": {"w": 2}, "b": {"w": 2}}),          # decode.go:660-664: the merge overwrites the earlier key
+    ("a: &a {w: 2}\nb: {w: 3, <<: *a, z: 1}\n", {"a": {"w": 2}, "b": {"w": 2, "z": 1}}),
+    ("a: &a {w: 2}\nb:\n  \"<<\": *a\n", {"a": {"w": 2}, "b": {"<<": {"w": 2}}}),      # a quoted "<<" is an ordinary key
     # anchors on scalars, sequences and nested blocks
-    ("x: &s hello\ny: *s\nz: [*s, *s]\n", {"x": "hello", "y": "hello", "z": ["hello", "hello"]}),
+    ("x: &s hello\nw: *s\nz: [*s, *s]\n", {"x": "hello", "w": "hello", "z": ["hello", "hello"]}),
     ("l: &l\n- 1\n- 2\nm: *l\n", {"l": [1, 2], "m": [1, 2]}),
     ("- &m\n  k: v\n- *m\n", [{"k": "v"}, {"k": "v"}]),
     # block scalars: clip / strip / keep, indentation indicator, blank and more-indented lines, '#' is content
@@ -173,6 +173,9 @@ HAND = [
     # numbers as yaml.v2 resolves them (resolve.go:147-190): ParseInt with base 0 after stripping '_', then yamlStyleFloat
     ("- 017\n- 0o17\n- 0b11\n- -0b11\n- 0x1F\n- 1_000\n- +12\n- 08\n- 1e3\n- 0E0\n- .5\n- 5.\n- _1\n- _\n- 1e\n- 0x\n- 1-2\n",
      [15, 15, 3, -3, 31, 1000, 12, 8.0, 1000.0, 0.0, 0.5, 5.0, "_1", "_", "1e", "0x", "1-2"]),
+    # mapping keys are resolved, then turned back into strings (sigs.k8s.io/yaml yaml.go:176-206)
+    ("010: a\nyes: b\n\"no\": c\nplain: d\nm: {0x10: e, Off: f, \"010\": g}\n",
+     {"8": "a", "true": "b", "no": "c", "plain": "d", "m": {"16": "e", "false": "f", "010": "g"}}),
     # directives, explicit start with a value, document end, a second document (ignored, like yaml.v2's Unmarshal)
     ("%YAML 1.1\n---\na: 1\n", {"a": 1}),
     ("--- \na: 1\n...\n", {"a": 1}),
@@ -190,6 +193,7 @@ def test_hand_written_documents(text, want):
 
 @pytest.mark.parametrize("text,needle", [
     ("a: *nope\n", "unknown anchor"),
+    ("~: x\n", "unsupported map key"),
     ("a: &x 1\nb:\n  <<: *x\n", "map merge requires"),
     ("a: !!binary aGk=\n", "unsupported YAML feature"),
     ("a: |x\n  t\n", "bad block scalar header"),
