@@ -84,9 +84,76 @@ bool yaml_style_float(const std::string &s) {
     return i == n;
 }
 
+// yaml.v2 parseTimestamp (resolve.go:224-258): an unquoted scalar that starts "dddd-" and parses under one of four Go layouts
+// ("2006-1-2T15:4:5.999999999Z07:00", the same with 't', "2006-1-2 15:4:5.999999999", "2006-1-2") is a time value; on its way
+// through sigs.k8s.io/yaml it becomes the JSON string time.Time marshals to (RFC 3339, nanoseconds trimmed).  Returns false if
+// `s` is not such a timestamp.
+bool go_timestamp(const std::string &s, std::string *rfc3339) {
+    size_t i = 0;
+    while (i < s.size() && std::isdigit((unsigned char)s[i])) i++;
+    if (i != 4 || i == s.size() || s[i] != '-') return false;
+    auto num = [&](size_t &p, int min_digits, int max_digits, int *out) {
+        int n = 0, v = 0;
+        while (p < s.size() && n < max_digits && std::isdigit((unsigned char)s[p])) { v = v * 10 + (s[p] - '0'); p++; n++; }
+        *out = v;
+        return n >= min_digits;
+    };
+    size_t p = 0;
+    int year, month, day, hour = 0, minute = 0, second = 0;
+    std::string frac, zone = "Z";
+    if (!num(p, 4, 4, &year) || p >= s.size() || s[p++] != '-') return false;
+    if (!num(p, 1, 2, &month) || p >= s.size() || s[p++] != '-') return false;
+    if (!num(p, 1, 2, &day)) return false;
+    if (p < s.size()) {
+        const char sep = s[p++];
+        if (sep != 'T' && sep != 't' && sep != ' ') return false;
+        if (!num(p, 1, 2, &hour) || p >= s.size() || s[p++] != ':') return false;
+        if (!num(p, 1, 2, &minute) || p >= s.size() || s[p++] != ':') return false;
+        if (!num(p, 1, 2, &second)) return false;
+        if (p < s.size() && s[p] == '.' && p + 1 < s.size() && std::isdigit((unsigned char)s[p + 1])) {
+            p++;
+            while (p < s.size() && std::isdigit((unsigned char)s[p])) frac += s[p++];
+            if (frac.size() > 9) frac.resize(9);  // time.Parse keeps nanoseconds
+            while (!frac.empty() && frac.back() == '0') frac.pop_back();
+        }
+        if (sep == ' ') {
+            if (p != s.size()) return false;  // the space form carries no zone
+        } else {
+            if (p >= s.size()) return false;  // the T forms need one
+            if (s[p] == 'Z') {
+                p++;
+            } else if (s[p] == '+' || s[p] == '-') {
+                const char sign = s[p++];
+                int zh, zm;
+                size_t q = p;
+                if (!num(q, 2, 2, &zh) || q >= s.size() || s[q++] != ':' || !num(q, 2, 2, &zm)) return false;
+                if (zh > 24 || zm > 60) return false;
+                p = q;
+                if (zh != 0 || zm != 0) {
+                    char buf[32];
+                    snprintf(buf, sizeof buf, "%c%02d:%02d", sign, zh, zm);
+                    zone = buf;
+                }
+            } else {
+                return false;
+            }
+            if (p != s.size()) return false;
+        }
+    }
+    static const int kDays[] = {31, 28, 31, 30, 31, 30, 31, 31, 30, 31, 30, 31};
+    const bool leap = (year % 4 == 0 && year % 100 != 0) || year % 400 == 0;
+    if (month < 1 || month > 12 || day < 1 || day > kDays[month - 1] + ((month == 2 && leap) ? 1 : 0)) return false;
+    if (hour > 23 || minute > 59 || second > 59) return false;
+    char buf[96];
+    snprintf(buf, sizeof buf, "%04d-%02d-%02dT%02d:%02d:%02d", year, month, day, hour, minute, second);
+    *rfc3339 = std::string(buf) + (frac.empty() ? "" : "." + frac) + zone;
+    return true;
+}
+
 // yaml.v2 resolve() (resolve.go:86-207) for a plain scalar with no tag: the fixed map of null / bool / inf / nan words, then by
 // first character: a digit or a sign -> int (Go base-0 syntax, so 017 is 15 and 0b11 is 3), unsigned, float by yamlStyleFloat;
-// a dot -> float; anything else a string.  Not done: the timestamp forms (2001-12-14 ...), which stay strings here.
+// a dot -> float; anything else a string.  Timestamps (2001-12-14 ...) come out as the RFC 3339 string the reference's
+// YAML -> JSON step turns them into.
 Value resolve_plain(const std::string &s) {
     Value v;
     if (s.empty() || s == "~" || s == "null" || s == "Null" || s == "NULL") return v;
@@ -114,6 +181,13 @@ Value resolve_plain(const std::string &s) {
         return as_string();
     }
     if (!(std::isdigit((unsigned char)c0) || c0 == '+' || c0 == '-')) return as_string();
+    std::string stamp;
+    if (go_timestamp(s, &stamp)) {
+        v.kind = Value::String;
+        v.s = stamp;
+        v.quoted = true;  // a JSON string from here on: no further coercion
+        return v;
+    }
     std::string plain;
     for (char c : s) if (c != '_') plain += c;
     bool neg = false;

@@ -173,6 +173,11 @@ HAND = [
     # numbers as yaml.v2 resolves them (resolve.go:147-190): ParseInt with base 0 after stripping '_', then yamlStyleFloat
     ("- 017\n- 0o17\n- 0b11\n- -0b11\n- 0x1F\n- 1_000\n- +12\n- 08\n- 1e3\n- 0E0\n- .5\n- 5.\n- _1\n- _\n- 1e\n- 0x\n- 1-2\n",
      [15, 15, 3, -3, 31, 1000, 12, 8.0, 1000.0, 0.0, 0.5, 5.0, "_1", "_", "1e", "0x", "1-2"]),
+    # timestamps (yaml.v2 resolve.go:224-258) arrive as the RFC 3339 string the reference's YAML -> JSON step makes of them
+    ("- 2001-12-14\n- 2001-12-14T21:59:43.10-05:00\n- 2001-12-14t21:59:43.1Z\n- 2001-12-14 21:59:43.10\n- 2001-2-3\n- 2001-02-30\n"
+     "- 2024-gpu\n- 2001-12-14T21:59:43\n- \"2001-12-14\"\n- 2001-12-14T1:2:3+00:00\n",
+     ["2001-12-14T00:00:00Z", "2001-12-14T21:59:43.1-05:00", "2001-12-14T21:59:43.1Z", "2001-12-14T21:59:43.1Z", "2001-02-03T00:00:00Z",
+      "2001-02-30", "2024-gpu", "2001-12-14T21:59:43", "2001-12-14", "2001-12-14T01:02:03Z"]),
     # mapping keys are resolved, then turned back into strings (sigs.k8s.io/yaml yaml.go:176-206)
     ("010: a\nyes: b\n\"no\": c\nplain: d\nm: {0x10: e, Off: f, \"010\": g}\n",
      {"8": "a", "true": "b", "no": "c", "plain": "d", "m": {"16": "e", "false": "f", "010": "g"}}),
